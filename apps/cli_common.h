@@ -1,0 +1,203 @@
+// Shared plumbing for the contract binaries: whole-stdin tokenizer, image/array
+// file I/O, error exits.  The stdin protocols and file formats are the
+// reference's; this implementation reads stdin in one gulp and
+// parses numbers with <charconv> instead of scanf.
+#pragma once
+#include <charconv>
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+namespace cli {
+
+[[noreturn]] inline void die(const char* fmt, const char* a = "", const char* b = "") {
+  fprintf(stderr, "[ERROR] ");
+  fprintf(stderr, fmt, a, b);
+  fprintf(stderr, "\n");
+  exit(1);
+}
+
+struct Input {
+  std::vector<char> buf;
+  const char* p = nullptr;
+  const char* end = nullptr;
+
+  void slurp(FILE* f) {
+    size_t cap = 1 << 20, len = 0;
+    buf.resize(cap);
+    for (;;) {
+      size_t got = fread(buf.data() + len, 1, cap - len, f);
+      len += got;
+      if (got == 0) break;
+      if (len == cap) buf.resize(cap *= 2);
+    }
+    buf.resize(len + 1);
+    buf[len] = 0;
+    p = buf.data();
+    end = p + len;
+  }
+  void skip_ws() {
+    while (p < end && (*p == ' ' || *p == '\n' || *p == '\t' || *p == '\r' || *p == '\v' ||
+                       *p == '\f'))
+      ++p;
+  }
+  bool eof() {
+    skip_ws();
+    return p >= end;
+  }
+  bool next_i64(long long& v) {
+    skip_ws();
+    if (p < end && *p == '+') ++p;
+    auto r = std::from_chars(p, end, v);
+    if (r.ec != std::errc()) return false;
+    p = r.ptr;
+    return true;
+  }
+  bool next_int(int& v) {
+    long long t;
+    if (!next_i64(t)) return false;
+    v = (int)t;
+    return true;
+  }
+  bool next_f64(double& v) {
+    skip_ws();
+    if (p < end && *p == '+') ++p;
+    auto r = std::from_chars(p, end, v);
+    if (r.ec == std::errc()) {
+      p = r.ptr;
+      return true;
+    }
+    // anything <charconv> refuses that scanf("%lf") takes (hex floats, overflow)
+    char* e = nullptr;
+    v = strtod(p, &e);
+    if (e == p) return false;
+    p = e;
+    return true;
+  }
+  bool next_f32(float& v) {
+    double d;
+    skip_ws();
+    // float-precision parse (scanf("%f") semantics), with the same fallback
+    if (p < end && *p == '+') ++p;
+    auto r = std::from_chars(p, end, v);
+    if (r.ec == std::errc()) {
+      p = r.ptr;
+      return true;
+    }
+    char* e = nullptr;
+    d = strtod(p, &e);
+    if (e == p) return false;
+    v = (float)d;
+    p = e;
+    return true;
+  }
+  bool next_word(std::string& s) {
+    skip_ws();
+    if (p >= end) return false;
+    const char* b = p;
+    while (p < end && !(*p == ' ' || *p == '\n' || *p == '\t' || *p == '\r')) ++p;
+    s.assign(b, p);
+    return true;
+  }
+};
+
+// ---- image files: int w, int h, RGBA bytes row-major (ref: lab2/src/main.cu:61-66)
+struct Image {
+  int w = 0, h = 0;
+  std::vector<uint32_t> px;
+};
+
+inline Image read_image(const std::string& path) {
+  FILE* f = fopen(path.c_str(), "rb");
+  if (!f) die("cannot open input image '%s'", path.c_str());
+  Image im;
+  if (fread(&im.w, 4, 1, f) != 1 || fread(&im.h, 4, 1, f) != 1) die("'%s': no w/h header", path.c_str());
+  if (im.w <= 0 || im.h <= 0) die("'%s': non-positive image size", path.c_str());
+  size_t n = (size_t)im.w * im.h;
+  im.px.resize(n);
+  if (fread(im.px.data(), 4, n, f) != n) die("'%s': truncated pixel data", path.c_str());
+  fclose(f);
+  return im;
+}
+
+inline void write_image(const std::string& path, int w, int h, const uint32_t* px) {
+  FILE* f = fopen(path.c_str(), "wb");
+  if (!f) die("cannot open output image '%s'", path.c_str());
+  size_t n = (size_t)w * h;
+  if (fwrite(&w, 4, 1, f) != 1 || fwrite(&h, 4, 1, f) != 1 || fwrite(px, 4, n, f) != n)
+    die("short write to '%s'", path.c_str());
+  fclose(f);
+}
+
+// ---- buffered number printing ("%.10e " / "%.6e " compatible)
+struct Out {
+  std::vector<char> buf;
+  size_t len = 0;
+  FILE* f;
+  explicit Out(FILE* f_) : buf(1 << 20), f(f_) {}
+  void flush() {
+    fwrite(buf.data(), 1, len, f);
+    len = 0;
+  }
+  template <typename T>
+  void sci(T v, int prec) {
+    if (len + 64 > buf.size()) flush();
+    auto r = std::to_chars(buf.data() + len, buf.data() + buf.size(), v,
+                           std::chars_format::scientific, prec);
+    len = (size_t)(r.ptr - buf.data());
+    buf[len++] = ' ';
+  }
+  ~Out() { flush(); }
+};
+
+}  // namespace cli
+
+#ifdef __CUDACC__
+#include <cuda_runtime.h>
+// Same report format as the reference's CSC macro (ref: lab1/src/main.cu:5-13).
+#define CSC(call)                                                                      \
+  do {                                                                                 \
+    cudaError_t _st = (call);                                                          \
+    if (_st != cudaSuccess) {                                                          \
+      fprintf(stderr, "[ERROR CUDA] File: '%s'; Line: %i; Message: %s.\n", __FILE__,   \
+              __LINE__, cudaGetErrorString(_st));                                      \
+      exit(1);                                                                         \
+    }                                                                                  \
+  } while (0)
+#define LIBOK(call)                                                                    \
+  do {                                                                                 \
+    if ((call) != 0) {                                                                 \
+      fprintf(stderr, "[ERROR CUDA] %s\n", b200_last_error());                         \
+      exit(1);                                                                         \
+    }                                                                                  \
+  } while (0)
+
+namespace cli {
+// cudaEvent pair around `fn`, after an untimed warm-up of the same launch unless
+// B200LABS_COLD=1 asks for the reference's cold single-shot timing.
+template <typename F>
+float time_device_ms(F&& fn, bool allow_warmup = true) {
+  const char* cold = getenv("B200LABS_COLD");
+  if (allow_warmup && !(cold && cold[0] == '1')) {
+    fn();
+    CSC(cudaDeviceSynchronize());
+  }
+  cudaEvent_t a, b;
+  CSC(cudaEventCreate(&a));
+  CSC(cudaEventCreate(&b));
+  CSC(cudaEventRecord(a));
+  fn();
+  CSC(cudaEventRecord(b));
+  CSC(cudaEventSynchronize(b));
+  CSC(cudaGetLastError());
+  float ms = 0;
+  CSC(cudaEventElapsedTime(&ms, a, b));
+  CSC(cudaEventDestroy(a));
+  CSC(cudaEventDestroy(b));
+  return ms;
+}
+}  // namespace cli
+#endif

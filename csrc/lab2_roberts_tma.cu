@@ -1,0 +1,245 @@
+// lab2, TMA variant: persistent CTAs, one per SM.  A producer warp keeps a ring
+// of kStages TMA tile loads in flight (cp.async.bulk.tensor -> UTMALDG); sixteen
+// consumer warps wait on the tile's mbarrier, run the stencil out of shared
+// memory and hand their 128 px x 4 row result block to the TMA store engine
+// (UTMASTG) from a private double-buffered staging area, so no CTA-wide barrier
+// is ever taken: the only synchronisation is the full/empty mbarrier pair per
+// stage and the per-thread bulk-group wait of the storing lane.
+//
+// A tile is 256 x 32 output pixels and is loaded as a self-contained
+// (256+4) x (32+1) box (element type u64 = 2 px so the 260-px row fits the
+// 256-element box limit): the +1 row / +1 column the stencil looks at come with
+// the tile, zero-filled by TMA outside the image and patched to clamp-to-edge /
+// the neighbour GPU's halo row by the consumer.  TMA stores clip partial tiles.
+// ref: lab2/src/main.cu:15-52 (same arithmetic, see roberts_math.cuh).
+#include <cuda.h>
+
+#include "common.cuh"
+#include "roberts_math.cuh"
+
+namespace b200 {
+
+constexpr int kTileW = 256;               // output px per tile row
+constexpr int kTileH = 32;                // output rows per tile
+constexpr int kBoxW = kTileW + 4;         // loaded px per row (260 -> 130 u64)
+constexpr int kBoxH = kTileH + 1;         // loaded rows
+constexpr int kPitch = kBoxW * 4;         // 1040 B, 16-byte multiple
+constexpr int kStageBytes = kPitch * kBoxH;  // 34320
+constexpr int kStageStride = 34816;       // 128-byte aligned slot
+constexpr int kStages = 4;
+constexpr int kConsumerWarps = 16;        // 2 column halves x 8 row groups of 4
+constexpr int kSubW = 128, kSubH = 4;     // per-warp output block
+constexpr int kOutBytes = kSubW * 4 * kSubH;  // 2048
+constexpr int kTmaThreads = (kConsumerWarps + 1) * 32;
+constexpr int kSmemBytes =
+    kStages * kStageStride + kConsumerWarps * 2 * kOutBytes + 2 * kStages * 8 + 128;
+
+struct TmaParams {
+  const uint32_t* below;  // row after the band (maybe on a peer GPU), never null
+  int64_t h_local;
+  int w;
+  int tiles_x;
+  int64_t n_tiles;
+};
+
+__global__ void __launch_bounds__(kTmaThreads, 1)
+    roberts_tma_kernel(const __grid_constant__ CUtensorMap in_map,
+                       const __grid_constant__ CUtensorMap out_map, TmaParams P) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  uint8_t* in_tiles = smem;
+  uint8_t* out_stage = smem + kStages * kStageStride;
+  uint64_t* full = (uint64_t*)(out_stage + kConsumerWarps * 2 * kOutBytes);
+  uint64_t* empty = full + kStages;
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < kStages; ++s) {
+      mbar_init(&full[s], 1);
+      mbar_init(&empty[s], kConsumerWarps);
+    }
+    mbar_fence_init();
+  }
+  __syncthreads();
+
+  if (warp == kConsumerWarps) {
+    // ===================== producer warp: one lane feeds the ring =============
+    if (lane == 0) {
+      prefetch_tmap(&in_map);
+      int it = 0;
+      for (int64_t t = blockIdx.x; t < P.n_tiles; t += gridDim.x, ++it) {
+        const int s = it % kStages;
+        const uint32_t ph = (it / kStages) & 1;
+        mbar_wait(&empty[s], ph ^ 1);
+        const int tx = (int)(t % P.tiles_x);
+        const int64_t ty = t / P.tiles_x;
+        mbar_expect_tx(&full[s], kStageBytes);
+        // coordinates: innermost in u64 elements (2 px), then rows
+        tma_load_2d(in_tiles + s * kStageStride, &in_map, tx * (kTileW / 2), (int)(ty * kTileH),
+                    &full[s]);
+      }
+    }
+    return;
+  }
+
+  // ========================= consumer warps ====================================
+  prefetch_tmap(&out_map);
+  const int chalf = warp & 1;       // which 128-px half of the tile
+  const int rgrp = warp >> 1;       // rows rgrp*4 .. rgrp*4+3
+  uint8_t* my_out = out_stage + warp * 2 * kOutBytes;
+  int it = 0;
+  for (int64_t t = blockIdx.x; t < P.n_tiles; t += gridDim.x, ++it) {
+    const int s = it % kStages;
+    const uint32_t ph = (it / kStages) & 1;
+    const int tx = (int)(t % P.tiles_x);
+    const int64_t ty = t / P.tiles_x;
+    const int x = tx * kTileW + chalf * kSubW + lane * 4;  // global column of this lane
+    const int64_t y0 = ty * kTileH + rgrp * kSubH;         // global row of this warp's block
+    const bool has_right = x + 4 < P.w;
+    const uint8_t* tile = in_tiles + s * kStageStride + (rgrp * kSubH) * kPitch +
+                          (chalf * kSubW + lane * 4) * 4;
+
+    if (y0 >= P.h_local || tx * kTileW + chalf * kSubW >= P.w) {
+      // block entirely outside the image (partial tile): just release the stage
+      mbar_wait(&full[s], ph);
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&empty[s]);
+      continue;
+    }
+    // the halo row of the band's last row is not in the tensor: fetch it early
+    const bool needs_below = y0 + kSubH >= P.h_local;
+    uint4 below_px = make_uint4(0, 0, 0, 0);
+    uint32_t below_edge = 0;
+    if (needs_below) {
+      if (x < P.w) below_px = ld_stream_u4(P.below + x);
+      if (lane == 31 && has_right) below_edge = ld_stream_u32(P.below + x + 4);
+    }
+
+    mbar_wait(&full[s], ph);
+
+    uint4 px[kSubH + 1];
+    uint32_t edge[kSubH + 1];
+#pragma unroll
+    for (int r = 0; r <= kSubH; ++r) {
+      px[r] = *(const uint4*)(tile + r * kPitch);
+      edge[r] = (lane == 31) ? *(const uint32_t*)(tile + r * kPitch + 16) : 0u;
+    }
+    if (needs_below) {
+#pragma unroll
+      for (int r = 1; r <= kSubH; ++r)
+        if (y0 + r == P.h_local) {
+          px[r] = below_px;
+          edge[r] = below_edge;
+        }
+    }
+    // all shared-memory reads of this stage are in registers: release it
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&empty[s]);
+
+    // staging buffer (it & 1) was handed to the TMA store two tiles ago
+    if (lane == 0) tma_store_wait_read<1>();
+    __syncwarp();
+    uint4* ob = (uint4*)(my_out + (it & 1) * kOutBytes) + lane;
+
+    float c0 = luma_rgba(px[0].x), c1 = luma_rgba(px[0].y), c2 = luma_rgba(px[0].z),
+          c3 = luma_rgba(px[0].w);
+    float c4 = __shfl_down_sync(0xffffffffu, c0, 1);
+    if (lane == 31) c4 = luma_rgba(edge[0]);
+    if (!has_right) c4 = c3;
+#pragma unroll
+    for (int r = 1; r <= kSubH; ++r) {
+      float n0 = luma_rgba(px[r].x), n1 = luma_rgba(px[r].y), n2 = luma_rgba(px[r].z),
+            n3 = luma_rgba(px[r].w);
+      float n4 = __shfl_down_sync(0xffffffffu, n0, 1);
+      if (lane == 31) n4 = luma_rgba(edge[r]);
+      if (!has_right) n4 = n3;
+      uint4 o;
+      o.x = roberts_pack(c0, c1, n0, n1, px[r - 1].x);
+      o.y = roberts_pack(c1, c2, n1, n2, px[r - 1].y);
+      o.z = roberts_pack(c2, c3, n2, n3, px[r - 1].z);
+      o.w = roberts_pack(c3, c4, n3, n4, px[r - 1].w);
+      ob[(r - 1) * (kSubW / 4)] = o;
+      c0 = n0, c1 = n1, c2 = n2, c3 = n3, c4 = n4;
+    }
+    fence_proxy_async_smem();  // generic-proxy writes -> visible to the TMA engine
+    __syncwarp();
+    if (lane == 0) {
+      tma_store_2d(&out_map, my_out + (it & 1) * kOutBytes, tx * kTileW + chalf * kSubW, (int)y0);
+      tma_store_commit();
+    }
+  }
+  if (lane == 0) tma_store_wait<0>();
+}
+
+// ---- host side ---------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                  const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn encode_fn() {
+  static EncodeTiledFn fn = [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) !=
+            cudaSuccess ||
+        q != cudaDriverEntryPointSuccess)
+      p = nullptr;
+    return (EncodeTiledFn)p;
+  }();
+  return fn;
+}
+
+bool roberts_tma_supported(const void* in, const void* out, int w, int64_t h_local) {
+  return w % 4 == 0 && w >= kTileW && h_local >= 1 && h_local < (1ll << 31) &&
+         ((((uintptr_t)in) | ((uintptr_t)out)) & 15u) == 0;
+}
+
+int roberts_tma_launch(const void* in, void* out, int w, int64_t h_local, const void* below_row,
+                       cudaStream_t st) {
+  EncodeTiledFn enc = encode_fn();
+  B200_REQUIRE(enc != nullptr, "roberts_tma: cuTensorMapEncodeTiled is not available");
+  CUtensorMap in_map, out_map;
+  {
+    cuuint64_t dims[2] = {(cuuint64_t)(w / 2), (cuuint64_t)h_local};
+    cuuint64_t strides[1] = {(cuuint64_t)w * 4};
+    cuuint32_t box[2] = {kBoxW / 2, kBoxH};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = enc(&in_map, CU_TENSOR_MAP_DATA_TYPE_UINT64, 2, (void*)in, dims, strides, box,
+                     estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                     CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    B200_REQUIRE(r == CUDA_SUCCESS, "roberts_tma: encode(in) failed with CUresult %d", (int)r);
+  }
+  {
+    cuuint64_t dims[2] = {(cuuint64_t)w, (cuuint64_t)h_local};
+    cuuint64_t strides[1] = {(cuuint64_t)w * 4};
+    cuuint32_t box[2] = {kSubW, kSubH};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = enc(&out_map, CU_TENSOR_MAP_DATA_TYPE_UINT32, 2, out, dims, strides, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                     CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    B200_REQUIRE(r == CUDA_SUCCESS, "roberts_tma: encode(out) failed with CUresult %d", (int)r);
+  }
+  TmaParams P;
+  P.below = (const uint32_t*)below_row;
+  P.h_local = h_local;
+  P.w = w;
+  P.tiles_x = (w + kTileW - 1) / kTileW;
+  P.n_tiles = (int64_t)P.tiles_x * ((h_local + kTileH - 1) / kTileH);
+  static bool attr_set[64] = {false};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (!attr_set[dev & 63]) {
+    B200_CUDA_OK(cudaFuncSetAttribute(roberts_tma_kernel,
+                                      cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+    attr_set[dev & 63] = true;
+  }
+  int64_t grid = device_info().sm_count;
+  if (grid > P.n_tiles) grid = P.n_tiles;
+  roberts_tma_kernel<<<(int)grid, kTmaThreads, kSmemBytes, st>>>(in_map, out_map, P);
+  B200_LAUNCH_OK();
+  return 0;
+}
+
+}  // namespace b200

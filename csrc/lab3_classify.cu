@@ -1,0 +1,332 @@
+// lab3: per-pixel Mahalanobis classifier.
+// ref: lab3/src/main.cu:40-76 (classify_kernel: fp64 quadratic form per pixel per
+// class, strict-< argmin, class index written into the alpha byte) and
+// :102-152 (class mean / covariance / inverse computed ON THE HOST).
+//
+// B200 design:
+//  * statistics on the device as EXACT 64-bit integer moments (n, S, SS) — integer
+//    sums are associative, so any sharding of the sample points over CTAs or GPUs
+//    gives bit-identical parameters (the multi-GPU path all-reduces these ten
+//    integers per class inside the kernel, see mgpu_lab3.cu);
+//  * DIRECT classify: 4 pixels per thread (one 128-bit load/store), parameters in
+//    shared memory, the reference's DFMA chain verbatim (fp64-pipe bound);
+//  * LUT classify: an RGBA8 image has at most 2^24 distinct colours, so for big
+//    images classify every colour once with the same DFMA chain into a 16 MiB
+//    table that lives in the 126 MB L2, then the image pass is a byte gather at
+//    HBM speed.  Decisions are bit-identical to DIRECT by construction.
+#include <cfloat>
+
+#include "common.cuh"
+
+namespace b200 {
+
+constexpr int kNP = B200_LAB3_PARAMS;
+constexpr int kNM = B200_LAB3_MOMENTS;
+constexpr int kMaxC = B200_LAB3_MAX_CLASSES;
+
+// ------------------------------------------------------------------ statistics
+constexpr int kMomThreads = 256;
+
+__global__ void __launch_bounds__(kMomThreads)
+    lab3_moments_kernel(const uint32_t* __restrict__ img, int w, int64_t y0, int64_t h_local,
+                        const int2* __restrict__ pts, const int* __restrict__ class_off,
+                        unsigned long long* __restrict__ moments) {
+  const int c = blockIdx.y;
+  const int begin = class_off[c], end = class_off[c + 1];
+  unsigned long long m[kNM];
+#pragma unroll
+  for (int k = 0; k < kNM; ++k) m[k] = 0;
+  for (int i = begin + blockIdx.x * kMomThreads + threadIdx.x; i < end;
+       i += gridDim.x * kMomThreads) {
+    const int2 p = __ldg(pts + i);
+    const int64_t yl = (int64_t)p.y - y0;
+    if (yl < 0 || yl >= h_local || p.x < 0 || p.x >= w) continue;  // another band owns it
+    const uint32_t px = __ldg(img + yl * w + p.x);
+    const unsigned r = px & 0xff, g = (px >> 8) & 0xff, b = (px >> 16) & 0xff;
+    m[0] += 1;
+    m[1] += r, m[2] += g, m[3] += b;
+    m[4] += r * r, m[5] += r * g, m[6] += r * b;
+    m[7] += g * g, m[8] += g * b, m[9] += b * b;
+  }
+  __shared__ unsigned long long red[kMomThreads / 32][kNM];
+#pragma unroll
+  for (int k = 0; k < kNM; ++k) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) m[k] += __shfl_down_sync(0xffffffffu, m[k], o);
+  }
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (lane == 0) {
+#pragma unroll
+    for (int k = 0; k < kNM; ++k) red[warp][k] = m[k];
+  }
+  __syncthreads();
+  if (threadIdx.x < kNM) {
+    unsigned long long s = 0;
+    for (int wv = 0; wv < kMomThreads / 32; ++wv) s += red[wv][threadIdx.x];
+    if (s) atomicAdd(moments + (size_t)c * kNM + threadIdx.x, s);
+  }
+}
+
+// moments -> mean + inverse covariance.  Same formulas as b200_cpu_lab3_finalize
+// (oracle.cpp); every product/sum uses an explicit-rounding intrinsic so nothing
+// is contracted and host and device agree bit for bit.
+__device__ void lab3_finalize_class(const long long* m, double* out) {
+  const long long n = m[0];
+  const double dn = (double)n;
+  out[0] = __ddiv_rn((double)m[1], dn);
+  out[1] = __ddiv_rn((double)m[2], dn);
+  out[2] = __ddiv_rn((double)m[3], dn);
+  const long long S[3] = {m[1], m[2], m[3]};
+  const int pair[3][3] = {{4, 5, 6}, {5, 7, 8}, {6, 8, 9}};
+  const double denom = (double)(n * (n - 1));
+  double cov[3][3];
+  for (int a = 0; a < 3; ++a)
+    for (int b = 0; b < 3; ++b) {
+      long long num = n * m[pair[a][b]] - S[a] * S[b];
+      cov[a][b] = __ddiv_rn((double)num, denom);
+    }
+  auto mul = [](double x, double y) { return __dmul_rn(x, y); };
+  auto sub = [](double x, double y) { return __dsub_rn(x, y); };
+  double det =
+      __dadd_rn(sub(mul(cov[0][0], sub(mul(cov[1][1], cov[2][2]), mul(cov[2][1], cov[1][2]))),
+                    mul(cov[0][1], sub(mul(cov[1][0], cov[2][2]), mul(cov[1][2], cov[2][0])))),
+                mul(cov[0][2], sub(mul(cov[1][0], cov[2][1]), mul(cov[1][1], cov[2][0]))));
+  for (int a = 0; a < 3; ++a)
+    for (int b = 0; b < 3; ++b) {
+      int b1 = (b + 1) % 3, b2 = (b + 2) % 3, a1 = (a + 1) % 3, a2 = (a + 2) % 3;
+      out[3 + a * 3 + b] =
+          __ddiv_rn(sub(mul(cov[b1][a1], cov[b2][a2]), mul(cov[b1][a2], cov[b2][a1])), det);
+    }
+}
+
+__global__ void lab3_finalize_kernel(const long long* __restrict__ moments, int nc,
+                                     double* __restrict__ params) {
+  int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c < nc) lab3_finalize_class(moments + (size_t)c * kNM, params + (size_t)c * kNP);
+}
+
+// ------------------------------------------------------------------- classify
+// distance of colour (r,g,b) to one class: the reference's operation chain
+//   temp[i] = fma(d2,m[2][i], fma(d1,m[1][i], fma(d0,m[0][i], 0)))
+//   dist    = fma(d2,temp[2], fma(d1,temp[1], fma(d0,temp[0], 0)))
+__device__ __forceinline__ double maha(double r, double g, double b, const double* p) {
+  const double d0 = __dsub_rn(r, p[0]), d1 = __dsub_rn(g, p[1]), d2 = __dsub_rn(b, p[2]);
+  double t0 = __fma_rn(d0, p[3], 0.0), t1 = __fma_rn(d0, p[4], 0.0), t2 = __fma_rn(d0, p[5], 0.0);
+  t0 = __fma_rn(d1, p[6], t0), t1 = __fma_rn(d1, p[7], t1), t2 = __fma_rn(d1, p[8], t2);
+  t0 = __fma_rn(d2, p[9], t0), t1 = __fma_rn(d2, p[10], t1), t2 = __fma_rn(d2, p[11], t2);
+  double dist = __fma_rn(d0, t0, 0.0);
+  dist = __fma_rn(d1, t1, dist);
+  return __fma_rn(d2, t2, dist);
+}
+
+template <int NPX>
+__device__ __forceinline__ void classify_group(const uint32_t (&px)[NPX], int nc,
+                                               const double* sp, int (&best)[NPX]) {
+  double r[NPX], g[NPX], b[NPX], mind[NPX];
+#pragma unroll
+  for (int k = 0; k < NPX; ++k) {
+    r[k] = (double)(px[k] & 0xff);
+    g[k] = (double)((px[k] >> 8) & 0xff);
+    b[k] = (double)((px[k] >> 16) & 0xff);
+    mind[k] = DBL_MAX;
+    best[k] = -1;
+  }
+  for (int c = 0; c < nc; ++c) {
+    double p[kNP];
+#pragma unroll
+    for (int j = 0; j < kNP; ++j) p[j] = sp[c * kNP + j];
+#pragma unroll
+    for (int k = 0; k < NPX; ++k) {
+      const double d = maha(r[k], g[k], b[k], p);
+      if (d < mind[k]) {
+        mind[k] = d;
+        best[k] = c;
+      }
+    }
+  }
+}
+
+__device__ __forceinline__ uint32_t set_alpha(uint32_t px, int cls) {
+  return (px & 0x00ffffffu) | ((uint32_t)(cls & 0xff) << 24);
+}
+
+__device__ __forceinline__ void load_params_smem(double* sp, const double* params, int nc) {
+  for (int i = threadIdx.x; i < nc * kNP; i += blockDim.x) sp[i] = params[i];
+  __syncthreads();
+}
+
+constexpr int kClsThreads = 256;
+
+// DIRECT: 4 px per thread, persistent grid-stride over 16-byte groups.
+__global__ void __launch_bounds__(kClsThreads)
+    lab3_classify_direct_kernel(uint32_t* __restrict__ img, int64_t n_vec, int nc,
+                                const double* __restrict__ params) {
+  __shared__ double sp[kMaxC * kNP];
+  load_params_smem(sp, params, nc);
+  const int64_t stride = (int64_t)gridDim.x * kClsThreads;
+  for (int64_t i = (int64_t)blockIdx.x * kClsThreads + threadIdx.x; i < n_vec; i += stride) {
+    uint4 v = *reinterpret_cast<const uint4*>(img + 4 * i);
+    uint32_t px[4] = {v.x, v.y, v.z, v.w};
+    int best[4];
+    classify_group<4>(px, nc, sp, best);
+    v.x = set_alpha(v.x, best[0]);
+    v.y = set_alpha(v.y, best[1]);
+    v.z = set_alpha(v.z, best[2]);
+    v.w = set_alpha(v.w, best[3]);
+    *reinterpret_cast<uint4*>(img + 4 * i) = v;
+  }
+}
+
+// scalar: tail pixels, unaligned images and the launch-geometry sweep
+__global__ void lab3_classify_scalar_kernel(uint32_t* __restrict__ img, int64_t begin, int64_t n,
+                                            int nc, const double* __restrict__ params) {
+  __shared__ double sp[kMaxC * kNP];
+  load_params_smem(sp, params, nc);
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = begin + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    uint32_t px[1] = {img[i]};
+    int best[1];
+    classify_group<1>(px, nc, sp, best);
+    img[i] = set_alpha(px[0], best[0]);
+  }
+}
+
+// LUT build: thread t classifies colours 4t..4t+3 (R fastest) -> one 32-bit store
+__global__ void __launch_bounds__(kClsThreads)
+    lab3_lut_build_kernel(uint32_t* __restrict__ lut4, int nc, const double* __restrict__ params) {
+  __shared__ double sp[kMaxC * kNP];
+  load_params_smem(sp, params, nc);
+  const uint32_t t = blockIdx.x * kClsThreads + threadIdx.x;  // 2^22 threads
+  uint32_t px[4] = {4 * t, 4 * t + 1, 4 * t + 2, 4 * t + 3};  // colour id == low 24 bits
+  int best[4];
+  classify_group<4>(px, nc, sp, best);
+  lut4[t] = (uint32_t)(best[0] & 0xff) | ((uint32_t)(best[1] & 0xff) << 8) |
+            ((uint32_t)(best[2] & 0xff) << 16) | ((uint32_t)(best[3] & 0xff) << 24);
+}
+
+// LUT apply: 4 px per thread, byte gathers through the read-only path
+__global__ void __launch_bounds__(kClsThreads)
+    lab3_lut_apply_kernel(uint32_t* __restrict__ img, int64_t n_vec,
+                          const uint8_t* __restrict__ lut) {
+  const int64_t stride = (int64_t)gridDim.x * kClsThreads;
+  for (int64_t i = (int64_t)blockIdx.x * kClsThreads + threadIdx.x; i < n_vec; i += stride) {
+    uint4 v = ld_stream_u4(img + 4 * i);
+    const uint32_t c0 = __ldg(lut + (v.x & 0xffffffu)), c1 = __ldg(lut + (v.y & 0xffffffu)),
+                   c2 = __ldg(lut + (v.z & 0xffffffu)), c3 = __ldg(lut + (v.w & 0xffffffu));
+    v.x = (v.x & 0xffffffu) | (c0 << 24);
+    v.y = (v.y & 0xffffffu) | (c1 << 24);
+    v.z = (v.z & 0xffffffu) | (c2 << 24);
+    v.w = (v.w & 0xffffffu) | (c3 << 24);
+    st_stream_u4(img + 4 * i, v);
+  }
+}
+
+__global__ void lab3_lut_apply_scalar_kernel(uint32_t* __restrict__ img, int64_t begin, int64_t n,
+                                             const uint8_t* __restrict__ lut) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = begin + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    uint32_t v = img[i];
+    img[i] = (v & 0xffffffu) | ((uint32_t)__ldg(lut + (v & 0xffffffu)) << 24);
+  }
+}
+
+constexpr size_t kLutBytes = size_t(1) << 24;
+constexpr int64_t kLutMinPixels = int64_t(1) << 25;
+
+static int pick_variant(int64_t npix, int variant, size_t scratch_bytes) {
+  if (variant != B200_CLASSIFY_AUTO) return variant;
+  return (npix >= kLutMinPixels && scratch_bytes >= kLutBytes) ? B200_CLASSIFY_LUT
+                                                               : B200_CLASSIFY_DIRECT;
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" int b200_lab3_moments(const void* img, int w, int64_t y0, int64_t h_local,
+                                 const int* pts, const int* class_off, int nc, long long* moments,
+                                 b200_stream_t s) {
+  B200_REQUIRE(nc > 0 && nc <= kMaxC, "lab3: class count %d outside 1..%d", nc, kMaxC);
+  // class sizes live on the device; size the grid for the documented maximum
+  // (2^19 points per class) — blocks past a class's end exit immediately.
+  dim3 grid(64, nc);
+  lab3_moments_kernel<<<grid, kMomThreads, 0, as_stream(s)>>>(
+      (const uint32_t*)img, w, y0, h_local, (const int2*)pts, class_off,
+      (unsigned long long*)moments);
+  B200_LAUNCH_OK();
+  return 0;
+}
+
+extern "C" int b200_lab3_finalize(const long long* moments, int nc, double* params,
+                                  b200_stream_t s) {
+  B200_REQUIRE(nc > 0 && nc <= kMaxC, "lab3: class count %d outside 1..%d", nc, kMaxC);
+  lab3_finalize_kernel<<<1, 32, 0, as_stream(s)>>>(moments, nc, params);
+  B200_LAUNCH_OK();
+  return 0;
+}
+
+extern "C" size_t b200_lab3_classify_scratch_bytes(int64_t npix, int variant) {
+  if (variant == B200_CLASSIFY_LUT) return kLutBytes;
+  if (variant == B200_CLASSIFY_AUTO && npix >= kLutMinPixels) return kLutBytes;
+  return 0;
+}
+
+extern "C" int b200_lab3_classify(void* img, int64_t npix, int nc, const double* params,
+                                  int variant, void* scratch, size_t scratch_bytes,
+                                  b200_stream_t s) {
+  B200_REQUIRE(nc > 0 && nc <= kMaxC, "lab3: class count %d outside 1..%d", nc, kMaxC);
+  if (npix <= 0) return 0;
+  cudaStream_t st = as_stream(s);
+  if (!scratch) scratch_bytes = 0;
+  variant = pick_variant(npix, variant, scratch_bytes);
+  const int sms = device_info().sm_count;
+  const bool aligned = (((uintptr_t)img) & 15u) == 0;
+  const int64_t n_vec = aligned ? npix / 4 : 0;
+  const int64_t tail = n_vec * 4;
+  auto grid_for = [&](int64_t items, int per_sm) {
+    int64_t want = (items + kClsThreads - 1) / kClsThreads;
+    int64_t cap = (int64_t)sms * per_sm;
+    return (int)(want < cap ? (want > 0 ? want : 1) : cap);
+  };
+  if (variant == B200_CLASSIFY_LUT) {
+    B200_REQUIRE(scratch_bytes >= kLutBytes, "lab3: LUT variant needs %zu bytes of scratch",
+                 kLutBytes);
+    lab3_lut_build_kernel<<<(1 << 22) / kClsThreads, kClsThreads, 0, st>>>((uint32_t*)scratch, nc,
+                                                                           params);
+    B200_LAUNCH_OK();
+    if (n_vec) {
+      lab3_lut_apply_kernel<<<grid_for(n_vec, 8), kClsThreads, 0, st>>>((uint32_t*)img, n_vec,
+                                                                        (const uint8_t*)scratch);
+      B200_LAUNCH_OK();
+    }
+    if (tail < npix) {
+      lab3_lut_apply_scalar_kernel<<<grid_for(npix - tail, 8), kClsThreads, 0, st>>>(
+          (uint32_t*)img, tail, npix, (const uint8_t*)scratch);
+      B200_LAUNCH_OK();
+    }
+    return 0;
+  }
+  B200_REQUIRE(variant == B200_CLASSIFY_DIRECT, "lab3: unknown classify variant %d", variant);
+  if (n_vec) {
+    lab3_classify_direct_kernel<<<grid_for(n_vec, 4), kClsThreads, 0, st>>>((uint32_t*)img, n_vec,
+                                                                            nc, params);
+    B200_LAUNCH_OK();
+  }
+  if (tail < npix) {
+    lab3_classify_scalar_kernel<<<grid_for(npix - tail, 4), kClsThreads, 0, st>>>(
+        (uint32_t*)img, tail, npix, nc, params);
+    B200_LAUNCH_OK();
+  }
+  return 0;
+}
+
+extern "C" int b200_lab3_classify_geom(void* img, int64_t npix, int nc, const double* params,
+                                       int blocks, int threads, b200_stream_t s) {
+  B200_REQUIRE(nc > 0 && nc <= kMaxC, "lab3: class count %d outside 1..%d", nc, kMaxC);
+  B200_REQUIRE(blocks > 0 && threads > 0, "lab3: launch dims must be positive (%d, %d)", blocks,
+               threads);
+  lab3_classify_scalar_kernel<<<blocks, threads, 0, as_stream(s)>>>((uint32_t*)img, 0, npix, nc,
+                                                                    params);
+  B200_LAUNCH_OK();
+  return 0;
+}

@@ -1,0 +1,385 @@
+// lab5: large-array ascending sort (int32 / uint32 / float32 / uint8 keys).
+// The reference ships only lab5/data/{int10,float10,uchar10} and no program, so
+// this lab is designed here; no CUB/Thrust — every kernel is in this file.
+//
+// B200 design: least-significant-digit radix sort, 8-bit digits, "onesweep":
+//   1. one histogram kernel reads the keys once and builds all four digit
+//      histograms (privatised per warp in shared memory);
+//   2. per pass ONE kernel ranks and scatters: tiles of 8192 keys take a ticket,
+//      rank their keys with warp match-any, publish the tile's digit counts and
+//      resolve their global offsets by decoupled look-back over earlier tiles
+//      (single 64-bit status|pass|value words, so no fences and one zero-fill
+//      serves all four passes), stage the keys in shared memory in digit order and
+//      write them out in coalesced runs.
+// Traffic: 1 read + 4 x (read + write) of the keys = 9 x 4 B per key, plus
+// ~2 KB of look-back words per 32 KB tile.  uint8 keys are a counting sort
+// (histogram + fill).
+#include "common.cuh"
+
+namespace b200 {
+
+constexpr int kRadixBits = 8;
+constexpr int kRadix = 1 << kRadixBits;
+constexpr int kSortThreads = 512;
+constexpr int kSortWarps = kSortThreads / 32;
+constexpr int kItems = 16;
+constexpr int kTile = kSortThreads * kItems;  // 8192 keys
+
+// order-preserving bijection key bits -> unsigned
+template <int KT>
+__device__ __forceinline__ uint32_t to_ordered(uint32_t k) {
+  if (KT == B200_KEY_I32) return k ^ 0x80000000u;
+  if (KT == B200_KEY_F32) return (k & 0x80000000u) ? ~k : (k | 0x80000000u);
+  return k;
+}
+
+// --------------------------------------------------------------- histograms
+constexpr int kHistThreads = 256;
+template <int KT>
+__global__ void __launch_bounds__(kHistThreads)
+    sort_hist_kernel(const uint32_t* __restrict__ keys, size_t n,
+                     unsigned long long* __restrict__ hist /* [4][256] */) {
+  __shared__ uint32_t sh[kHistThreads / 32][4][kRadix];  // 32 KB, one copy per warp
+  uint32_t* flat = &sh[0][0][0];
+  for (int i = threadIdx.x; i < (kHistThreads / 32) * 4 * kRadix; i += kHistThreads) flat[i] = 0;
+  __syncthreads();
+  uint32_t(*my)[kRadix] = sh[threadIdx.x >> 5];
+  auto add = [&](uint32_t k) {
+    const uint32_t o = to_ordered<KT>(k);
+    atomicAdd(&my[0][o & 0xff], 1u);
+    atomicAdd(&my[1][(o >> 8) & 0xff], 1u);
+    atomicAdd(&my[2][(o >> 16) & 0xff], 1u);
+    atomicAdd(&my[3][o >> 24], 1u);
+  };
+  const size_t n_vec = (((uintptr_t)keys) & 15u) == 0 ? n / 4 : 0;
+  const size_t stride = (size_t)gridDim.x * kHistThreads;
+  // bounded trip count per block keeps the 32-bit shared counters from overflowing
+  for (size_t i = (size_t)blockIdx.x * kHistThreads + threadIdx.x; i < n_vec; i += stride) {
+    const uint4 v = ld_stream_u4(keys + 4 * i);
+    add(v.x), add(v.y), add(v.z), add(v.w);
+  }
+  for (size_t i = n_vec * 4 + (size_t)blockIdx.x * kHistThreads + threadIdx.x; i < n; i += stride)
+    add(keys[i]);
+  __syncthreads();
+  for (int i = threadIdx.x; i < 4 * kRadix; i += kHistThreads) {
+    unsigned long long s = 0;
+    for (int wv = 0; wv < kHistThreads / 32; ++wv) s += sh[wv][i >> 8][i & 0xff];
+    if (s) atomicAdd(hist + i, s);
+  }
+}
+
+// exclusive scan of each 256-bin histogram, in place: hist[p][d] -> first output
+// index of digit d in pass p
+__global__ void sort_scan_kernel(unsigned long long* __restrict__ hist, int passes) {
+  __shared__ unsigned long long wsum[kRadix / 32];
+  for (int p = 0; p < passes; ++p) {
+    unsigned long long v = hist[p * kRadix + threadIdx.x];
+    unsigned long long inc = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      unsigned long long t = __shfl_up_sync(0xffffffffu, inc, o);
+      if ((threadIdx.x & 31) >= o) inc += t;
+    }
+    if ((threadIdx.x & 31) == 31) wsum[threadIdx.x >> 5] = inc;
+    __syncthreads();
+    unsigned long long base = 0;
+    for (int wv = 0; wv < (int)(threadIdx.x >> 5); ++wv) base += wsum[wv];
+    hist[p * kRadix + threadIdx.x] = base + inc - v;
+    __syncthreads();
+  }
+}
+
+// ------------------------------------------------------------------ onesweep
+constexpr unsigned long long kStatusShift = 62, kPassShift = 58;
+constexpr unsigned long long kValueMask = (1ull << kPassShift) - 1;
+constexpr unsigned long long kStAggregate = 1, kStInclusive = 2;
+
+__device__ __forceinline__ unsigned long long ld_lookback(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_lookback(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
+struct SweepSmem {
+  uint32_t keys[kTile];                   // 32 KB: keys in digit order
+  uint32_t warp_hist[kSortWarps][kRadix]; // 16 KB: per-warp digit counts -> offsets
+  unsigned long long global_off[kRadix];  // output index of (digit, tile-position 0)
+  uint32_t tile_start[kRadix];            // first tile position of each digit
+  uint32_t scan_tmp[kRadix / 32];
+  uint32_t tile_id;
+};
+
+template <int KT>
+__global__ void __launch_bounds__(kSortThreads, 2)
+    sort_onesweep_kernel(const uint32_t* __restrict__ in, uint32_t* __restrict__ out, size_t n,
+                         int pass, const unsigned long long* __restrict__ digit_base /*[256]*/,
+                         unsigned long long* __restrict__ lookback /*[tiles][256]*/,
+                         uint32_t* __restrict__ ticket) {
+  extern __shared__ __align__(16) uint8_t smem_raw[];
+  SweepSmem& S = *reinterpret_cast<SweepSmem*>(smem_raw);
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int shift = pass * kRadixBits;
+
+  if (tid == 0) S.tile_id = atomicAdd(ticket, 1u);
+  for (int i = tid; i < kSortWarps * kRadix; i += kSortThreads) (&S.warp_hist[0][0])[i] = 0;
+  __syncthreads();
+  const uint32_t tile = S.tile_id;
+  const size_t tile_base = (size_t)tile * kTile;
+  const uint32_t n_valid = (uint32_t)min((size_t)kTile, n - tile_base);
+
+  // ---- load: warp-striped, logical order == memory order (keeps the pass stable)
+  uint32_t key[kItems];
+  const uint32_t w_off = warp * (kItems * 32) + lane;
+#pragma unroll
+  for (int i = 0; i < kItems; ++i) {
+    const uint32_t o = w_off + i * 32;
+    key[i] = o < n_valid ? ld_stream_u32(in + tile_base + o) : 0xffffffffu;
+  }
+
+  // ---- rank inside the warp: match-any on the digit, leader bumps the counter
+  uint16_t rank[kItems];
+  uint32_t* wh = S.warp_hist[warp];
+  const uint32_t lt_mask = (1u << lane) - 1;
+#pragma unroll
+  for (int i = 0; i < kItems; ++i) {
+    const bool valid = (w_off + i * 32) < n_valid;
+    // padding keys rank as digit 255 *after* every real key (they come last)
+    const uint32_t d = valid ? ((to_ordered<KT>(key[i]) >> shift) & 0xff) : 0xffu;
+    const uint32_t peers = __match_any_sync(0xffffffffu, d);
+    const int leader = __ffs(peers) - 1;
+    uint32_t old = 0;
+    if (lane == leader) {
+      old = wh[d];
+      wh[d] = old + __popc(peers);
+    }
+    old = __shfl_sync(0xffffffffu, old, leader);
+    rank[i] = (uint16_t)(old + __popc(peers & lt_mask));
+    __syncwarp();
+  }
+  __syncthreads();
+
+  // ---- per digit: scan over warps, publish the tile aggregate, look back
+  uint32_t count = 0;
+  if (tid < kRadix) {
+#pragma unroll
+    for (int wv = 0; wv < kSortWarps; ++wv) {
+      const uint32_t c = S.warp_hist[wv][tid];
+      S.warp_hist[wv][tid] = count;  // exclusive offset of this warp inside the digit
+      count += c;
+    }
+    uint32_t real = count;
+    if (tid == kRadix - 1) real -= (kTile - n_valid);  // drop the padding keys
+    const unsigned long long tag = ((unsigned long long)pass << kPassShift);
+    st_lookback(lookback + (size_t)tile * kRadix + tid, (kStAggregate << kStatusShift) | tag | real);
+
+    // exclusive scan of `count` over the 256 digits -> tile_start
+    uint32_t inc = count;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+      if (lane >= o) inc += t;
+    }
+    if (lane == 31) S.scan_tmp[warp] = inc;
+    asm volatile("bar.sync 1, 256;" ::: "memory");
+    uint32_t base = 0;
+    for (int wv = 0; wv < warp; ++wv) base += S.scan_tmp[wv];
+    const uint32_t start = base + inc - count;
+    S.tile_start[tid] = start;
+
+    // decoupled look-back: sum aggregates of earlier tiles until an inclusive one
+    unsigned long long excl = 0;
+    for (int64_t t = (int64_t)tile - 1; t >= 0;) {
+      const unsigned long long e = ld_lookback(lookback + (size_t)t * kRadix + tid);
+      const unsigned long long st = e >> kStatusShift;
+      if (st == 0 || ((e >> kPassShift) & 0xf) != (unsigned long long)pass) continue;  // not yet
+      excl += e & kValueMask;
+      if (st == kStInclusive) break;
+      --t;
+    }
+    st_lookback(lookback + (size_t)tile * kRadix + tid,
+                (kStInclusive << kStatusShift) | tag | (excl + real));
+    S.global_off[tid] = digit_base[tid] + excl - start;
+  }
+  __syncthreads();
+
+  // ---- stage keys in digit order
+#pragma unroll
+  for (int i = 0; i < kItems; ++i) {
+    const bool valid = (w_off + i * 32) < n_valid;
+    const uint32_t d = valid ? ((to_ordered<KT>(key[i]) >> shift) & 0xff) : 0xffu;
+    S.keys[S.tile_start[d] + S.warp_hist[warp][d] + rank[i]] = key[i];
+  }
+  __syncthreads();
+
+  // ---- coalesced runs out
+#pragma unroll
+  for (int i = 0; i < kItems; ++i) {
+    const uint32_t p = tid + i * kSortThreads;
+    if (p < n_valid) {
+      const uint32_t k = S.keys[p];
+      const uint32_t d = (to_ordered<KT>(k) >> shift) & 0xff;
+      out[S.global_off[d] + p] = k;
+    }
+  }
+}
+
+// ------------------------------------------------------------------ uint8 keys
+__global__ void __launch_bounds__(kHistThreads)
+    sort_u8_hist_kernel(const uint8_t* __restrict__ keys, size_t n,
+                        unsigned long long* __restrict__ hist) {
+  __shared__ uint32_t sh[kHistThreads / 32][kRadix];
+  for (int i = threadIdx.x; i < (kHistThreads / 32) * kRadix; i += kHistThreads)
+    (&sh[0][0])[i] = 0;
+  __syncthreads();
+  uint32_t* my = sh[threadIdx.x >> 5];
+  const size_t n_vec = (((uintptr_t)keys) & 15u) == 0 ? n / 16 : 0;
+  const size_t stride = (size_t)gridDim.x * kHistThreads;
+  for (size_t i = (size_t)blockIdx.x * kHistThreads + threadIdx.x; i < n_vec; i += stride) {
+    const uint4 v = ld_stream_u4(keys + 16 * i);
+    const uint32_t wds[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      atomicAdd(&my[wds[k] & 0xff], 1u);
+      atomicAdd(&my[(wds[k] >> 8) & 0xff], 1u);
+      atomicAdd(&my[(wds[k] >> 16) & 0xff], 1u);
+      atomicAdd(&my[wds[k] >> 24], 1u);
+    }
+  }
+  for (size_t i = n_vec * 16 + (size_t)blockIdx.x * kHistThreads + threadIdx.x; i < n; i += stride)
+    atomicAdd(&my[keys[i]], 1u);
+  __syncthreads();
+  for (int i = threadIdx.x; i < kRadix; i += kHistThreads) {
+    unsigned long long s = 0;
+    for (int wv = 0; wv < kHistThreads / 32; ++wv) s += sh[wv][i];
+    if (s) atomicAdd(hist + i, s);
+  }
+}
+
+// out[i] = the digit whose [start, end) range holds i; starts come from the scan
+__global__ void __launch_bounds__(256)
+    sort_u8_fill_kernel(uint8_t* __restrict__ out, size_t n,
+                        const unsigned long long* __restrict__ starts) {
+  __shared__ unsigned long long st[kRadix + 1];
+  st[threadIdx.x] = starts[threadIdx.x];
+  if (threadIdx.x == 0) st[kRadix] = n;
+  __syncthreads();
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    int lo = 0, hi = kRadix;  // largest d with st[d] <= i
+    while (hi - lo > 1) {
+      const int mid = (lo + hi) >> 1;
+      if (st[mid] <= i) lo = mid; else hi = mid;
+    }
+    out[i] = (uint8_t)lo;
+  }
+}
+
+struct SortScratch {
+  unsigned long long* hist;      // [4][256]
+  uint32_t* tickets;             // [4] (+pad)
+  unsigned long long* lookback;  // [tiles][256]
+  size_t tiles;
+  size_t bytes;
+};
+
+static SortScratch carve(void* scratch, size_t n) {
+  SortScratch s;
+  uint8_t* p = (uint8_t*)scratch;
+  s.hist = (unsigned long long*)p;
+  p += 4 * kRadix * sizeof(unsigned long long);
+  s.tickets = (uint32_t*)p;
+  p += 64;
+  s.lookback = (unsigned long long*)p;
+  s.tiles = (n + kTile - 1) / kTile;
+  p += s.tiles * kRadix * sizeof(unsigned long long);
+  s.bytes = (size_t)(p - (uint8_t*)scratch);
+  return s;
+}
+
+template <int KT>
+static int sort32(uint32_t* keys, uint32_t* tmp, size_t n, const SortScratch& sc, cudaStream_t st) {
+  const int sms = device_info().sm_count;
+  static bool attr_set[64] = {false};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (!attr_set[dev & 63]) {
+    B200_CUDA_OK(cudaFuncSetAttribute(sort_onesweep_kernel<KT>,
+                                      cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      (int)sizeof(SweepSmem)));
+    attr_set[dev & 63] = true;
+  }
+  {
+    size_t want = (n / 4 + kHistThreads - 1) / kHistThreads + 1;
+    // >= sms*8 blocks and <= 2^22 keys per block (32-bit shared counters stay exact)
+    size_t min_blocks = (n >> 22) + 1;
+    size_t blocks = want < (size_t)sms * 8 ? want : (size_t)sms * 8;
+    if (blocks < min_blocks) blocks = min_blocks;
+    sort_hist_kernel<KT><<<(unsigned)blocks, kHistThreads, 0, st>>>(keys, n, sc.hist);
+    B200_LAUNCH_OK();
+  }
+  sort_scan_kernel<<<1, kRadix, 0, st>>>(sc.hist, 4);
+  B200_LAUNCH_OK();
+  uint32_t* src = keys;
+  uint32_t* dst = tmp;
+  for (int pass = 0; pass < 4; ++pass) {
+    sort_onesweep_kernel<KT><<<(unsigned)sc.tiles, kSortThreads, sizeof(SweepSmem), st>>>(
+        src, dst, n, pass, sc.hist + pass * kRadix, sc.lookback, sc.tickets + pass);
+    B200_LAUNCH_OK();
+    uint32_t* t = src;
+    src = dst;
+    dst = t;
+  }
+  return 0;  // four passes: the result is back in `keys`
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" size_t b200_sort_scratch_bytes(size_t n, int key_type) {
+  (void)key_type;
+  return carve(nullptr, n).bytes;
+}
+
+extern "C" int b200_sort(void* keys, void* tmp, size_t n, int key_type, void* scratch,
+                         size_t scratch_bytes, b200_stream_t s) {
+  if (n == 0) return 0;
+  cudaStream_t st = as_stream(s);
+  SortScratch sc = carve(scratch, n);
+  B200_REQUIRE(scratch && scratch_bytes >= sc.bytes, "sort: scratch too small (%zu < %zu bytes)",
+               scratch_bytes, sc.bytes);
+  B200_REQUIRE((((uintptr_t)scratch) & 15u) == 0, "sort: scratch must be 16-byte aligned");
+  B200_REQUIRE(n < (size_t(1) << 40), "sort: n too large");
+  B200_CUDA_OK(cudaMemsetAsync(scratch, 0, sc.bytes, st));
+  const int sms = device_info().sm_count;
+  switch (key_type) {
+    case B200_KEY_I32:
+      return sort32<B200_KEY_I32>((uint32_t*)keys, (uint32_t*)tmp, n, sc, st);
+    case B200_KEY_U32:
+      return sort32<B200_KEY_U32>((uint32_t*)keys, (uint32_t*)tmp, n, sc, st);
+    case B200_KEY_F32:
+      return sort32<B200_KEY_F32>((uint32_t*)keys, (uint32_t*)tmp, n, sc, st);
+    case B200_KEY_U8: {
+      size_t want = (n / 16 + kHistThreads - 1) / kHistThreads + 1;
+      size_t min_blocks = (n >> 24) + 1;
+      size_t blocks = want < (size_t)sms * 8 ? want : (size_t)sms * 8;
+      if (blocks < min_blocks) blocks = min_blocks;
+      sort_u8_hist_kernel<<<(unsigned)blocks, kHistThreads, 0, st>>>((const uint8_t*)keys, n,
+                                                                     sc.hist);
+      B200_LAUNCH_OK();
+      sort_scan_kernel<<<1, kRadix, 0, st>>>(sc.hist, 1);
+      B200_LAUNCH_OK();
+      size_t fb = (n + 255) / 256;
+      if (fb > (size_t)sms * 16) fb = (size_t)sms * 16;
+      sort_u8_fill_kernel<<<(unsigned)fb, 256, 0, st>>>((uint8_t*)keys, n, sc.hist);
+      B200_LAUNCH_OK();
+      return 0;
+    }
+    default:
+      B200_REQUIRE(false, "sort: unknown key type %d", key_type);
+  }
+  return 0;
+}

@@ -1,0 +1,127 @@
+/*
+ * b200labs.h — C ABI of libb200labs, the native layer of the B200 lab suite.
+ *
+ * Every kernel entry point takes raw device pointers plus a cudaStream_t (passed
+ * as void* so the header is usable from plain C and from ctypes), enqueues work
+ * on that stream and returns 0 on success or a non-zero code; the text of the
+ * last failure on the calling thread is available from b200_last_error().
+ * Nothing here synchronises the stream unless the comment says so.
+ *
+ * "ref:" comments name the file:line of KoryakovDmitry/cuda-mpi-openmp whose
+ * behaviour the entry point reproduces (relative to the reference root).
+ */
+#ifndef B200LABS_H
+#define B200LABS_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef void* b200_stream_t; /* cudaStream_t */
+
+/* ---------------------------------------------------------------- generic */
+const char* b200_last_error(void);
+int b200_version(void);
+/* Number of kernels this library has launched in the calling process. */
+uint64_t b200_launch_count(void);
+/* Device properties in the eight-line layout of ref: gpu_info/src/main.cu:9-16.
+ * Writes at most cap bytes (NUL-terminated) and returns the full length. */
+int b200_gpu_info(int device, char* buf, int cap, int extended);
+/* Writes > L2-size bytes so the next kernel starts cold (bench hygiene). */
+int b200_flush_l2(void* scratch, size_t bytes, b200_stream_t s);
+
+/* ------------------------------------------------------------------- lab1 */
+/* c[i] = a[i] - b[i] over doubles.  ref: lab1/src/main.cu:22-29 */
+int b200_vecsub_f64(const double* a, const double* b, double* c, size_t n,
+                    b200_stream_t s);
+/* Same result, launched as <<<grid, block>>> exactly as given (the harness's
+ * launch-geometry sweep).  ref: lab1/src/to_plot.cu:33-40,72 */
+int b200_vecsub_f64_geom(const double* a, const double* b, double* c, size_t n,
+                         int grid, int block, b200_stream_t s);
+
+/* ------------------------------------------------------------------- lab2 */
+/* Roberts-cross edge filter over RGBA8 pixels, clamp-to-edge, alpha kept.
+ * ref: lab2/src/main.cu:15-52 (kernel), :68-87 (clamp/point texture).
+ *
+ * in/out are row-major w x h_local bands of a taller image.  below_row is the
+ * row that follows the band (w pixels): NULL means the band ends the image and
+ * the last row is clamped; otherwise it may point into this GPU's memory or
+ * into a peer GPU's mapped memory (the row-sharded multi-GPU path reads the
+ * neighbour's first row through it from inside the kernel).
+ * variant: B200_ROBERTS_AUTO picks by shape. */
+enum {
+  B200_ROBERTS_AUTO = 0,
+  B200_ROBERTS_STREAM = 1, /* register sliding window, 128-bit accesses      */
+  B200_ROBERTS_TMA = 2,    /* TMA tile pipeline + cluster/DSMEM column share */
+  B200_ROBERTS_GENERIC = 3 /* one pixel per thread, any alignment            */
+};
+int b200_roberts(const void* in, void* out, int w, int64_t h_local,
+                 const void* below_row, int variant, b200_stream_t s);
+/* Launch-geometry sweep build: block (bx,by), grid (gx,gy) honoured as given.
+ * ref: lab2/src/to_plot.cu:57-64,106 */
+int b200_roberts_geom(const void* in, void* out, int w, int h, int bx, int by,
+                      int gx, int gy, b200_stream_t s);
+
+/* ------------------------------------------------------------------- lab3 */
+#define B200_LAB3_MAX_CLASSES 32
+#define B200_LAB3_MOMENTS 10 /* n, SR,SG,SB, SRR,SRG,SRB,SGG,SGB,SBB */
+#define B200_LAB3_PARAMS 12  /* avg[3], inv_cov[3][3] per class      */
+
+/* Exact integer moments of the sample pixels of each class.  pts holds (x,y)
+ * int pairs, class c owns pts[class_off[c] .. class_off[c+1]).  Only points
+ * whose y lies in [y0, y0+h_local) are gathered from img (a band that starts
+ * at global row y0); moments is int64[nc][10] and is ACCUMULATED into (zero it
+ * first).  New: the reference does this on the host, lab3/src/main.cu:102-117. */
+int b200_lab3_moments(const void* img, int w, int64_t y0, int64_t h_local,
+                      const int* pts, const int* class_off, int nc,
+                      long long* moments, b200_stream_t s);
+/* moments -> params[nc][12] = mean and inverse covariance (double), same
+ * determinant/adjugate formulas as ref: lab3/src/main.cu:117,137-150. */
+int b200_lab3_finalize(const long long* moments, int nc, double* params,
+                       b200_stream_t s);
+enum { B200_CLASSIFY_AUTO = 0, B200_CLASSIFY_DIRECT = 1, B200_CLASSIFY_LUT = 2 };
+/* bytes of scratch b200_lab3_classify needs for this variant/size (0 = none) */
+size_t b200_lab3_classify_scratch_bytes(int64_t npix, int variant);
+/* In place: alpha := argmin_c Mahalanobis(pixel, class c), lowest index wins
+ * ties.  params is device double[nc][12].  ref: lab3/src/main.cu:40-76 */
+int b200_lab3_classify(void* img, int64_t npix, int nc, const double* params,
+                       int variant, void* scratch, size_t scratch_bytes,
+                       b200_stream_t s);
+/* Launch-geometry sweep build <<<blocks, threads>>>. ref: lab3/src/to_plot.cu:76-81,162 */
+int b200_lab3_classify_geom(void* img, int64_t npix, int nc,
+                            const double* params, int blocks, int threads,
+                            b200_stream_t s);
+
+/* ------------------------------------------------------------------- lab5 */
+enum { B200_KEY_I32 = 0, B200_KEY_F32 = 1, B200_KEY_U8 = 2, B200_KEY_U32 = 3 };
+size_t b200_sort_scratch_bytes(size_t n, int key_type);
+/* Ascending sort of n keys.  keys is overwritten with the sorted result; tmp
+ * is a second buffer of the same size; scratch from b200_sort_scratch_bytes.
+ * (The reference ships only lab5/data/*, no program: this lab is new.) */
+int b200_sort(void* keys, void* tmp, size_t n, int key_type, void* scratch,
+              size_t scratch_bytes, b200_stream_t s);
+
+/* ------------------------------------------------------------- CPU oracles */
+/* Plain C++ restatements used by the tests and the CPU binaries. */
+void b200_cpu_vecsub_f64(const double* a, const double* b, double* c, size_t n);
+/* FMA-faithful to the contraction nvcc applies to ref: lab2/src/main.cu:30-40 */
+void b200_cpu_roberts(const void* in, void* out, int w, int h);
+/* Two-pass host statistics in input order, ref: lab3/src/main.cu:102-150 */
+void b200_cpu_lab3_stats_ref(const void* img, int w, const int* pts,
+                             const int* class_off, int nc, double* params);
+/* Integer-moment statistics (what the device path computes). */
+void b200_cpu_lab3_moments(const void* img, int w, int64_t y0, int64_t h_local,
+                           const int* pts, const int* class_off, int nc,
+                           long long* moments);
+void b200_cpu_lab3_finalize(const long long* moments, int nc, double* params);
+void b200_cpu_lab3_classify(void* img, int64_t npix, int nc,
+                            const double* params);
+void b200_cpu_sort(void* keys, size_t n, int key_type);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200LABS_H */
