@@ -38,7 +38,9 @@ constexpr int kHistThreads = 256;
 template <int KT>
 __global__ void __launch_bounds__(kHistThreads)
     sort_hist_kernel(const uint32_t* __restrict__ keys, size_t n,
+                     const unsigned long long* __restrict__ n_dev,
                      unsigned long long* __restrict__ hist /* [4][256] */) {
+  if (n_dev) n = (size_t)*n_dev;  // length decided on the device (multi-GPU bucket)
   __shared__ uint32_t sh[kHistThreads / 32][4][kRadix];  // 32 KB, one copy per warp
   uint32_t* flat = &sh[0][0][0];
   for (int i = threadIdx.x; i < (kHistThreads / 32) * 4 * kRadix; i += kHistThreads) flat[i] = 0;
@@ -115,7 +117,8 @@ struct SweepSmem {
 template <int KT>
 __global__ void __launch_bounds__(kSortThreads, 2)
     sort_onesweep_kernel(const uint32_t* __restrict__ in, uint32_t* __restrict__ out, size_t n,
-                         int pass, const unsigned long long* __restrict__ digit_base /*[256]*/,
+                         const unsigned long long* __restrict__ n_dev, int pass,
+                         const unsigned long long* __restrict__ digit_base /*[256]*/,
                          unsigned long long* __restrict__ lookback /*[tiles][256]*/,
                          uint32_t* __restrict__ ticket) {
   extern __shared__ __align__(16) uint8_t smem_raw[];
@@ -128,6 +131,8 @@ __global__ void __launch_bounds__(kSortThreads, 2)
   __syncthreads();
   const uint32_t tile = S.tile_id;
   const size_t tile_base = (size_t)tile * kTile;
+  if (n_dev) n = (size_t)*n_dev;
+  if (tile_base >= n) return;  // grid was sized for the capacity, not the actual length
   const uint32_t n_valid = (uint32_t)min((size_t)kTile, n - tile_base);
 
   // ---- load: warp-striped, logical order == memory order (keeps the pass stable)
@@ -300,7 +305,8 @@ static SortScratch carve(void* scratch, size_t n) {
 }
 
 template <int KT>
-static int sort32(uint32_t* keys, uint32_t* tmp, size_t n, const SortScratch& sc, cudaStream_t st) {
+static int sort32(const uint32_t* input, uint32_t* keys, uint32_t* tmp, size_t n,
+                  const unsigned long long* n_dev, const SortScratch& sc, cudaStream_t st) {
   const int sms = device_info().sm_count;
   static bool attr_set[64] = {false};
   int dev = 0;
@@ -317,22 +323,23 @@ static int sort32(uint32_t* keys, uint32_t* tmp, size_t n, const SortScratch& sc
     size_t min_blocks = (n >> 22) + 1;
     size_t blocks = want < (size_t)sms * 8 ? want : (size_t)sms * 8;
     if (blocks < min_blocks) blocks = min_blocks;
-    sort_hist_kernel<KT><<<(unsigned)blocks, kHistThreads, 0, st>>>(keys, n, sc.hist);
+    sort_hist_kernel<KT><<<(unsigned)blocks, kHistThreads, 0, st>>>(input, n, n_dev, sc.hist);
     B200_LAUNCH_OK();
   }
   sort_scan_kernel<<<1, kRadix, 0, st>>>(sc.hist, 4);
   B200_LAUNCH_OK();
-  uint32_t* src = keys;
+  // pass 0 reads the caller's input (which may be a separate, untouched buffer),
+  // then the passes ping-pong tmp <-> keys and the fourth one lands in `keys`
+  const uint32_t* src = input;
   uint32_t* dst = tmp;
   for (int pass = 0; pass < 4; ++pass) {
     sort_onesweep_kernel<KT><<<(unsigned)sc.tiles, kSortThreads, sizeof(SweepSmem), st>>>(
-        src, dst, n, pass, sc.hist + pass * kRadix, sc.lookback, sc.tickets + pass);
+        src, dst, n, n_dev, pass, sc.hist + pass * kRadix, sc.lookback, sc.tickets + pass);
     B200_LAUNCH_OK();
-    uint32_t* t = src;
     src = dst;
-    dst = t;
+    dst = (dst == tmp) ? keys : tmp;
   }
-  return 0;  // four passes: the result is back in `keys`
+  return 0;  // four passes: the result is in `keys`
 }
 
 }  // namespace b200
@@ -344,9 +351,29 @@ extern "C" size_t b200_sort_scratch_bytes(size_t n, int key_type) {
   return carve(nullptr, n).bytes;
 }
 
+// n is an upper bound (grid, scratch); when n_dev is non-null the actual length is
+// read from it on the device, so a producer kernel can decide it without a host sync.
+// `input` (optional, 32-bit keys only) is read instead of `keys` by the first pass
+// and left untouched, so a caller can sort out of place without a copy.
+extern "C" int b200_sort_ex(const void* input, void* keys, void* tmp, size_t n,
+                            const unsigned long long* n_dev, int key_type, void* scratch,
+                            size_t scratch_bytes, b200_stream_t s);
+
 extern "C" int b200_sort(void* keys, void* tmp, size_t n, int key_type, void* scratch,
                          size_t scratch_bytes, b200_stream_t s) {
+  return b200_sort_ex(nullptr, keys, tmp, n, nullptr, key_type, scratch, scratch_bytes, s);
+}
+
+extern "C" int b200_sort_devn(void* keys, void* tmp, size_t n, const unsigned long long* n_dev,
+                              int key_type, void* scratch, size_t scratch_bytes, b200_stream_t s) {
+  return b200_sort_ex(nullptr, keys, tmp, n, n_dev, key_type, scratch, scratch_bytes, s);
+}
+
+extern "C" int b200_sort_ex(const void* input, void* keys, void* tmp, size_t n,
+                            const unsigned long long* n_dev, int key_type, void* scratch,
+                            size_t scratch_bytes, b200_stream_t s) {
   if (n == 0) return 0;
+  if (!input) input = keys;
   cudaStream_t st = as_stream(s);
   SortScratch sc = carve(scratch, n);
   B200_REQUIRE(scratch && scratch_bytes >= sc.bytes, "sort: scratch too small (%zu < %zu bytes)",
@@ -357,12 +384,14 @@ extern "C" int b200_sort(void* keys, void* tmp, size_t n, int key_type, void* sc
   const int sms = device_info().sm_count;
   switch (key_type) {
     case B200_KEY_I32:
-      return sort32<B200_KEY_I32>((uint32_t*)keys, (uint32_t*)tmp, n, sc, st);
+      return sort32<B200_KEY_I32>((const uint32_t*)input, (uint32_t*)keys, (uint32_t*)tmp, n, n_dev, sc, st);
     case B200_KEY_U32:
-      return sort32<B200_KEY_U32>((uint32_t*)keys, (uint32_t*)tmp, n, sc, st);
+      return sort32<B200_KEY_U32>((const uint32_t*)input, (uint32_t*)keys, (uint32_t*)tmp, n, n_dev, sc, st);
     case B200_KEY_F32:
-      return sort32<B200_KEY_F32>((uint32_t*)keys, (uint32_t*)tmp, n, sc, st);
+      return sort32<B200_KEY_F32>((const uint32_t*)input, (uint32_t*)keys, (uint32_t*)tmp, n, n_dev, sc, st);
     case B200_KEY_U8: {
+      B200_REQUIRE(n_dev == nullptr && input == keys,
+                   "sort: device-side length / separate input are for 32-bit keys only");
       size_t want = (n / 16 + kHistThreads - 1) / kHistThreads + 1;
       size_t min_blocks = (n >> 24) + 1;
       size_t blocks = want < (size_t)sms * 8 ? want : (size_t)sms * 8;

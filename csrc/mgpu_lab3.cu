@@ -1,0 +1,141 @@
+// lab3, multi-GPU: class statistics all-reduced INSIDE the statistics kernel.
+//
+// The image is row-sharded; every rank gathers the sample pixels that fall into
+// its band and accumulates the ten exact integer moments per class.  The last CTA
+// to finish (ticket counter) pushes this rank's 32x10 partial sums straight into
+// every peer's slot over NVLink (plain remote stores), fences at system scope and
+// raises the peers' flags; it then waits for all peers' flags, adds the slots in
+// rank order and derives mean + inverse covariance — one launch per rank, no
+// collective library call.  Integer sums are associative, so 1, 2, 4 or 8 GPUs
+// produce bit-identical parameters.
+// phase_mask: 1 = accumulate + push + signal, 2 = wait + reduce + finalize, 3 = both
+// (the product path).  The split exists so that several virtual ranks can be
+// exercised on ONE GPU without kernels that wait on each other.
+// (ref: the reference computes these statistics on the host, lab3/src/main.cu:102-152,
+// and has no multi-GPU path.)
+#include "common.cuh"
+#include "lab3_math.cuh"
+#include "symm.cuh"
+
+namespace b200 {
+
+constexpr int kStatThreads = 256;
+
+__device__ __forceinline__ long long ld_cg_s64(const long long* p) {
+  long long v;
+  asm volatile("ld.global.cg.s64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+
+__global__ void __launch_bounds__(kStatThreads)
+    lab3_stats_allreduce_kernel(const uint32_t* __restrict__ img, int w, int64_t y0,
+                                int64_t h_local, const int2* __restrict__ pts,
+                                const int* __restrict__ class_off, int nc, SymmPeers peers,
+                                int rank, int world, uint64_t epoch, double* __restrict__ params,
+                                long long* __restrict__ moments_out, int phase_mask,
+                                unsigned long long timeout_ns) {
+  SymmWorkspace* me = peers.ws[rank];
+  __shared__ unsigned long long red[kStatThreads / 32][kLab3M];
+  __shared__ long long total[kLab3C][kLab3M];
+  __shared__ bool is_last;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int par = (int)(epoch & 1);
+
+  if (phase_mask & 1) {
+    // ---- accumulate this CTA's share of class blockIdx.y --------------------
+    const int c = blockIdx.y;
+    const int begin = class_off[c], end = class_off[c + 1];
+    unsigned long long m[kLab3M];
+#pragma unroll
+    for (int k = 0; k < kLab3M; ++k) m[k] = 0;
+    for (int i = begin + blockIdx.x * kStatThreads + tid; i < end; i += gridDim.x * kStatThreads) {
+      const int2 p = __ldg(pts + i);
+      const int64_t yl = (int64_t)p.y - y0;
+      if (yl < 0 || yl >= h_local || p.x < 0 || p.x >= w) continue;
+      const uint32_t px = __ldg(img + yl * w + p.x);
+      const unsigned r = px & 0xff, g = (px >> 8) & 0xff, b = (px >> 16) & 0xff;
+      m[0] += 1;
+      m[1] += r, m[2] += g, m[3] += b;
+      m[4] += r * r, m[5] += r * g, m[6] += r * b;
+      m[7] += g * g, m[8] += g * b, m[9] += b * b;
+    }
+#pragma unroll
+    for (int k = 0; k < kLab3M; ++k) {
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) m[k] += __shfl_down_sync(0xffffffffu, m[k], o);
+    }
+    if (lane == 0) {
+#pragma unroll
+      for (int k = 0; k < kLab3M; ++k) red[warp][k] = m[k];
+    }
+    __syncthreads();
+    if (tid < kLab3M) {
+      unsigned long long s = 0;
+      for (int wv = 0; wv < kStatThreads / 32; ++wv) s += red[wv][tid];
+      if (s) atomicAdd((unsigned long long*)&me->lab3_acc[c][tid], s);
+    }
+    // ---- ticket: the last CTA of the grid carries on -------------------------
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) {
+      const unsigned int n_blocks = gridDim.x * gridDim.y;
+      is_last = atomicAdd(&me->lab3_blocks_done, 1u) == n_blocks - 1;
+    }
+    __syncthreads();
+    if (!is_last) return;
+    __threadfence();
+    // ---- push my partial sums into every peer's slot (remote stores) ---------
+    for (int i = tid; i < nc * kLab3M; i += kStatThreads) {
+      long long* acc = &me->lab3_acc[0][0] + i;
+      const long long v = ld_cg_s64(acc);
+      *acc = 0;  // ready for the next call
+      for (int p = 0; p < world; ++p) (&peers.ws[p]->lab3_slots[par][rank][0][0])[i] = v;
+    }
+    if (tid == 0) me->lab3_blocks_done = 0;
+    __threadfence_system();
+    __syncthreads();
+    if (tid < world) {
+      __threadfence_system();
+      signal_peer(peers, tid, rank, epoch, kFlagLab3);
+    }
+  }
+
+  if (phase_mask & 2) {
+    // ---- wait for every rank's push, reduce in rank order, finalize ---------
+    if (tid < world) wait_peer(peers, rank, tid, epoch, timeout_ns, kFlagLab3);
+    __syncthreads();
+    for (int i = tid; i < nc * kLab3M; i += kStatThreads) {
+      long long s = 0;
+      for (int p = 0; p < world; ++p) s += ld_cg_s64(&me->lab3_slots[par][p][0][0] + i);
+      (&total[0][0])[i] = s;
+      if (moments_out) moments_out[i] = s;
+    }
+    __syncthreads();
+    if (tid < nc) lab3_finalize_class(total[tid], params + (size_t)tid * B200_LAB3_PARAMS);
+  }
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+// Fused statistics + all-reduce + finalize.  ws_ptrs: device array [world] of the
+// peer-mapped SymmWorkspace of every rank; epoch must grow by one per call (the
+// same value on every rank).  moments_out (optional) receives the reduced integers.
+extern "C" int b200_lab3_stats_allreduce(const void* img, int w, int64_t y0, int64_t h_local,
+                                         const int* pts, const int* class_off, int nc,
+                                         const void* ws_ptrs, int rank, int world,
+                                         uint64_t epoch, double* params, long long* moments_out,
+                                         int phase_mask, b200_stream_t s) {
+  B200_REQUIRE(nc > 0 && nc <= kLab3C, "lab3: class count %d outside 1..%d", nc, kLab3C);
+  B200_REQUIRE(world >= 1 && world <= kMaxWorld && rank >= 0 && rank < world,
+               "lab3: bad rank/world %d/%d", rank, world);
+  B200_REQUIRE(phase_mask >= 1 && phase_mask <= 3, "lab3: phase_mask must be 1, 2 or 3");
+  SymmPeers peers{(SymmWorkspace* const*)ws_ptrs};
+  dim3 grid = (phase_mask & 1) ? dim3(64, nc) : dim3(1, 1);
+  lab3_stats_allreduce_kernel<<<grid, kStatThreads, 0, as_stream(s)>>>(
+      (const uint32_t*)img, w, y0, h_local, (const int2*)pts, class_off, nc, peers, rank, world,
+      epoch, params, moments_out, phase_mask, kDefaultTimeoutNs);
+  B200_LAUNCH_OK();
+  return 0;
+}

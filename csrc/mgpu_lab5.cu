@@ -1,0 +1,340 @@
+// lab5, multi-GPU: sample sort whose key exchange is fused into the partitioning
+// kernel — every CTA classifies a tile of keys against the splitters, reserves
+// room in each destination GPU's bucket with one remote atomic per destination
+// and stores its keys straight into the peers' buckets over NVLink / NVSwitch.
+// No send buffers, no counts exchange, no collective call.
+//
+//   1. splitters_kernel (1 CTA per rank): stratified sample of the local keys,
+//      pushed as unique 64-bit composites (ordered key | source rank | index) into
+//      every peer's workspace, flag exchange, then each rank bitonic-sorts the
+//      identical sample set and keeps every S-th composite as a splitter.  The
+//      composites are unique, so equal keys are split between neighbouring ranks
+//      and heavily duplicated inputs stay balanced.
+//   2. partition_scatter_kernel: the fused partition + all-to-all described above;
+//      its last CTA (ticket) fences at system scope, signals all peers, waits for
+//      all peers and publishes the number of keys that landed in the local bucket.
+//   3. local radix sort of the bucket, its length read on the device (lab5_sort.cu).
+// The phase masks exist so that virtual ranks can be exercised on one GPU without
+// kernels waiting on each other.  (No counterpart in the reference.)
+#include "common.cuh"
+#include "symm.cuh"
+
+namespace b200 {
+
+template <int KT>
+__device__ __forceinline__ uint32_t to_ordered_mg(uint32_t k) {
+  if (KT == B200_KEY_I32) return k ^ 0x80000000u;
+  if (KT == B200_KEY_F32) return (k & 0x80000000u) ? ~k : (k | 0x80000000u);
+  return k;
+}
+
+__device__ __forceinline__ unsigned long long make_composite(uint32_t ordered, int src,
+                                                             unsigned long long idx, int idx_bits) {
+  return ((unsigned long long)ordered << 32) | ((unsigned long long)src << idx_bits) | idx;
+}
+
+__device__ __forceinline__ uint32_t hash32(uint32_t x) {
+  x ^= x >> 16, x *= 0x7feb352du, x ^= x >> 15, x *= 0x846ca68bu, x ^= x >> 16;
+  return x;
+}
+
+constexpr int kSplitThreads = 1024;
+
+template <int KT>
+__global__ void __launch_bounds__(kSplitThreads)
+    sort_splitters_kernel(const uint32_t* __restrict__ keys, unsigned long long n_local,
+                          int samples_per_rank, int idx_bits, SymmPeers peers, int rank, int world,
+                          uint64_t epoch, uint32_t seed, int phase_mask,
+                          unsigned long long timeout_ns) {
+  extern __shared__ unsigned long long sm[];  // world * samples_per_rank composites
+  SymmWorkspace* me = peers.ws[rank];
+  const int tid = threadIdx.x;
+  const int total = world * samples_per_rank;
+
+  if (phase_mask & 1) {
+    if (tid == 0) {
+      me->sort_cursor = 0;  // before anyone can learn my samples, hence before any scatter
+      me->sort_recv_count = 0;
+      me->sort_blocks_done = 0;
+    }
+    // stratified sample: one pseudo-random key out of each of S equal strata
+    for (int j = tid; j < samples_per_rank; j += kSplitThreads) {
+      unsigned long long comp = ~0ull;  // sorts last when the shard is empty
+      if (n_local > 0) {
+        const unsigned long long lo = n_local * (unsigned long long)j / samples_per_rank;
+        const unsigned long long hi = n_local * (unsigned long long)(j + 1) / samples_per_rank;
+        const unsigned long long idx =
+            hi > lo ? lo + hash32(seed ^ (uint32_t)(j * 0x9e3779b9u)) % (hi - lo) : min(lo, n_local - 1);
+        comp = make_composite(to_ordered_mg<KT>(keys[idx]), rank, idx, idx_bits);
+      }
+      for (int p = 0; p < world; ++p)
+        peers.ws[p]->sort_samples[rank * samples_per_rank + j] = comp;  // remote store
+    }
+    __threadfence_system();
+    __syncthreads();
+    if (tid < world) {
+      __threadfence_system();
+      signal_peer(peers, tid, rank, epoch, kFlagSortSamples);
+    }
+  }
+  if (phase_mask & 2) {
+    if (tid < world) wait_peer(peers, rank, tid, epoch, timeout_ns, kFlagSortSamples);
+    __syncthreads();
+    // bitonic sort of `total` (power of two) composites in shared memory
+    for (int i = tid; i < total; i += kSplitThreads) {
+      unsigned long long v;
+      asm volatile("ld.global.cg.u64 %0, [%1];" : "=l"(v) : "l"(me->sort_samples + i) : "memory");
+      sm[i] = v;
+    }
+    __syncthreads();
+    for (int k = 2; k <= total; k <<= 1) {
+      for (int j = k >> 1; j > 0; j >>= 1) {
+        for (int i = tid; i < total; i += kSplitThreads) {
+          const int ixj = i ^ j;
+          if (ixj > i) {
+            const unsigned long long a = sm[i], b = sm[ixj];
+            const bool up = (i & k) == 0;
+            if ((a > b) == up) {
+              sm[i] = b;
+              sm[ixj] = a;
+            }
+          }
+        }
+        __syncthreads();
+      }
+    }
+    if (tid < world) me->sort_splitters[tid] = tid == 0 ? 0ull : sm[tid * samples_per_rank];
+  }
+}
+
+// ---------------------------------------------------------- fused partition+exchange
+constexpr int kPartThreads = 512;
+constexpr int kPartWarps = kPartThreads / 32;
+constexpr int kPartItems = 16;
+constexpr int kPartTile = kPartThreads * kPartItems;  // 8192 keys
+
+struct PartTargets {
+  uint32_t* bucket[kMaxWorld];              // destination buckets (peer-mapped or local)
+  unsigned long long* cursor[kMaxWorld];    // their fill cursors (remote atomics)
+};
+
+template <int KT>
+__global__ void __launch_bounds__(kPartThreads, 2)
+    sort_partition_scatter_kernel(const uint32_t* __restrict__ keys, unsigned long long n_local,
+                                  const unsigned long long* __restrict__ splitters, int idx_bits,
+                                  PartTargets tg, unsigned long long capacity, SymmPeers peers,
+                                  int rank, int world, uint64_t epoch, int phase_mask,
+                                  unsigned long long timeout_ns) {
+  __shared__ uint32_t s_keys[kPartTile];
+  __shared__ uint32_t warp_cnt[kPartWarps][kMaxWorld];
+  __shared__ uint32_t tile_start[kMaxWorld + 1];
+  __shared__ unsigned long long base[kMaxWorld];
+  __shared__ unsigned long long s_split[kMaxWorld];
+  __shared__ bool is_last;
+  SymmWorkspace* me = peers.ws[rank];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+
+  if (phase_mask & 1) {
+    if (tid < kMaxWorld) s_split[tid] = tid < world ? splitters[tid] : ~0ull;
+    for (int i = tid; i < kPartWarps * kMaxWorld; i += kPartThreads) (&warp_cnt[0][0])[i] = 0;
+    __syncthreads();
+    const unsigned long long tile_base = (unsigned long long)blockIdx.x * kPartTile;
+    const uint32_t n_valid = (uint32_t)min((unsigned long long)kPartTile, n_local - tile_base);
+
+    uint32_t key[kPartItems];
+    uint8_t dst[kPartItems];
+    uint16_t rk[kPartItems];
+    const uint32_t w_off = warp * (kPartItems * 32) + lane;
+    const uint32_t lt_mask = (1u << lane) - 1;
+#pragma unroll
+    for (int i = 0; i < kPartItems; ++i) {
+      const uint32_t o = w_off + i * 32;
+      const bool valid = o < n_valid;
+      key[i] = valid ? ld_stream_u32(keys + tile_base + o) : 0u;
+      int d = 0;
+      if (valid) {
+        const unsigned long long comp =
+            make_composite(to_ordered_mg<KT>(key[i]), rank, tile_base + o, idx_bits);
+#pragma unroll
+        for (int k = 1; k < kMaxWorld; ++k) d += (k < world && s_split[k] <= comp) ? 1 : 0;
+      } else {
+        d = kMaxWorld;  // padding: no destination
+      }
+      dst[i] = (uint8_t)d;
+      const uint32_t peers_mask = __match_any_sync(0xffffffffu, d);
+      const int leader = __ffs(peers_mask) - 1;
+      uint32_t old = 0;
+      if (valid && lane == leader) {
+        old = warp_cnt[warp][d];
+        warp_cnt[warp][d] = old + __popc(peers_mask);
+      }
+      old = __shfl_sync(0xffffffffu, old, leader);
+      rk[i] = (uint16_t)(old + __popc(peers_mask & lt_mask));
+      __syncwarp();
+    }
+    __syncthreads();
+    // per destination: offsets of the warps, tile total, remote reservation
+    if (tid < world) {
+      uint32_t run = 0;
+      for (int wv = 0; wv < kPartWarps; ++wv) {
+        const uint32_t c = warp_cnt[wv][tid];
+        warp_cnt[wv][tid] = run;
+        run += c;
+      }
+      tile_start[tid + 1] = run;  // totals for now, scanned below
+      unsigned long long b = 0;
+      if (run) b = atomicAdd_system(tg.cursor[tid], (unsigned long long)run);
+      if (b + run > capacity) {
+        atomicOr(&me->error, (unsigned long long)kErrSortOverflow);
+        b = ~0ull;  // poison: this tile's keys for that destination are dropped
+      }
+      base[tid] = b;
+    }
+    __syncthreads();
+    if (tid == 0) {
+      tile_start[0] = 0;
+      for (int d = 0; d < world; ++d) tile_start[d + 1] += tile_start[d];
+    }
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < kPartItems; ++i) {
+      const int d = dst[i];
+      if (d < kMaxWorld) s_keys[tile_start[d] + warp_cnt[warp][d] + rk[i]] = key[i];
+    }
+    __syncthreads();
+    // runs of equal destination leave as contiguous remote stores
+#pragma unroll
+    for (int i = 0; i < kPartItems; ++i) {
+      const uint32_t p = tid + i * kPartThreads;
+      if (p < n_valid) {
+        int d = 0;
+#pragma unroll
+        for (int k = 1; k < kMaxWorld; ++k) d += (k < world && tile_start[k] <= p) ? 1 : 0;
+        const unsigned long long b = base[d];
+        if (b != ~0ull) tg.bucket[d][b + (p - tile_start[d])] = s_keys[p];
+      }
+    }
+    // ---- ticket: last CTA tells every peer that this rank has finished writing
+    __threadfence_system();
+    __syncthreads();
+    if (tid == 0) is_last = atomicAdd(&me->sort_blocks_done, 1u) == gridDim.x - 1;
+    __syncthreads();
+    if (!is_last) return;
+    if (!(phase_mask & 4)) {  // bit 2 set: local-only partition (NCCL baseline), no signalling
+      if (tid == 0) me->sort_blocks_done = 0;
+      __threadfence_system();
+      if (tid < world) signal_peer(peers, tid, rank, epoch, kFlagSortDone);
+    } else if (tid == 0) {
+      me->sort_blocks_done = 0;
+    }
+  }
+  if ((phase_mask & 2) && !(phase_mask & 4)) {
+    if (tid < world) wait_peer(peers, rank, tid, epoch, timeout_ns, kFlagSortDone);
+    __syncthreads();
+    if (tid == 0) {
+      unsigned long long c;
+      asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(c) : "l"(&me->sort_cursor) : "memory");
+      me->sort_recv_count = c < capacity ? c : capacity;
+    }
+  }
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+static int idx_bits_for(int world) {
+  int src_bits = 0;
+  while ((1 << src_bits) < world) ++src_bits;
+  return 32 - src_bits;
+}
+
+// Step 1 of the multi-GPU sort: sample, exchange, choose splitters (left in
+// ws[rank]->sort_splitters).  samples_per_rank * world must be a power of two <= 8192.
+extern "C" int b200_sort_mgpu_splitters(const void* keys, size_t n_local, int key_type,
+                                        int samples_per_rank, const void* ws_ptrs, int rank,
+                                        int world, uint64_t epoch, int phase_mask,
+                                        b200_stream_t s) {
+  B200_REQUIRE(world >= 1 && world <= kMaxWorld && rank >= 0 && rank < world,
+               "sort_mgpu: bad rank/world %d/%d", rank, world);
+  const int total = world * samples_per_rank;
+  B200_REQUIRE(samples_per_rank > 0 && total <= kSortMaxSamplesTotal && (total & (total - 1)) == 0,
+               "sort_mgpu: world*samples_per_rank must be a power of two <= %d (got %d)",
+               kSortMaxSamplesTotal, total);
+  const int idx_bits = idx_bits_for(world);
+  B200_REQUIRE(idx_bits >= 32 || n_local <= (1ull << idx_bits), "sort_mgpu: shard too large");
+  SymmPeers peers{(SymmWorkspace* const*)ws_ptrs};
+  const size_t smem = (size_t)total * sizeof(unsigned long long);
+  cudaStream_t st = as_stream(s);
+#define LAUNCH_SPLIT(KT)                                                                       \
+  do {                                                                                         \
+    B200_CUDA_OK(cudaFuncSetAttribute(sort_splitters_kernel<KT>,                               \
+                                      cudaFuncAttributeMaxDynamicSharedMemorySize, 65536));    \
+    sort_splitters_kernel<KT><<<1, kSplitThreads, smem, st>>>(                                 \
+        (const uint32_t*)keys, n_local, samples_per_rank, idx_bits, peers, rank, world, epoch, \
+        0x5bd1e995u, phase_mask, kDefaultTimeoutNs);                                           \
+  } while (0)
+  switch (key_type) {
+    case B200_KEY_I32: LAUNCH_SPLIT(B200_KEY_I32); break;
+    case B200_KEY_U32: LAUNCH_SPLIT(B200_KEY_U32); break;
+    case B200_KEY_F32: LAUNCH_SPLIT(B200_KEY_F32); break;
+    default: B200_REQUIRE(false, "sort_mgpu: 32-bit key types only (got %d)", key_type);
+  }
+#undef LAUNCH_SPLIT
+  B200_LAUNCH_OK();
+  return 0;
+}
+
+// Step 2: fused partition + all-to-all.  bucket_ptrs / cursor_ptrs: HOST arrays
+// [world] of device addresses (peer-mapped buckets and their uint64 fill cursors;
+// pass cursor_ptrs = NULL to use each rank's workspace cursor).  splitters: device
+// uint64[world] (normally &ws[rank]->sort_splitters).  phase_mask: 1 scatter+signal,
+// 2 wait+publish count, 4 (with 1) local partition only, no signalling.
+extern "C" int b200_sort_mgpu_scatter(const void* keys, size_t n_local, int key_type,
+                                      const void* splitters, void* const* bucket_ptrs,
+                                      void* const* cursor_ptrs, size_t capacity,
+                                      const void* ws_ptrs, void* const* ws_host_ptrs, int rank,
+                                      int world, uint64_t epoch, int phase_mask,
+                                      b200_stream_t s) {
+  B200_REQUIRE(world >= 1 && world <= kMaxWorld && rank >= 0 && rank < world,
+               "sort_mgpu: bad rank/world %d/%d", rank, world);
+  SymmPeers peers{(SymmWorkspace* const*)ws_ptrs};
+  PartTargets tg;
+  for (int p = 0; p < kMaxWorld; ++p) {
+    tg.bucket[p] = p < world ? (uint32_t*)bucket_ptrs[p] : nullptr;
+    if (p >= world)
+      tg.cursor[p] = nullptr;
+    else if (cursor_ptrs)
+      tg.cursor[p] = (unsigned long long*)cursor_ptrs[p];
+    else
+      tg.cursor[p] = &((SymmWorkspace*)ws_host_ptrs[p])->sort_cursor;
+  }
+  const int idx_bits = idx_bits_for(world);
+  B200_REQUIRE(n_local > 0, "sort_mgpu: empty shards are not supported");
+  const unsigned grid = (phase_mask & 1) ? (unsigned)((n_local + kPartTile - 1) / kPartTile) : 1u;
+  cudaStream_t st = as_stream(s);
+#define LAUNCH_PART(KT)                                                                         \
+  sort_partition_scatter_kernel<KT><<<grid, kPartThreads, 0, st>>>(                             \
+      (const uint32_t*)keys, n_local, (const unsigned long long*)splitters, idx_bits, tg,       \
+      capacity, peers, rank, world, epoch, phase_mask, kDefaultTimeoutNs)
+  switch (key_type) {
+    case B200_KEY_I32: LAUNCH_PART(B200_KEY_I32); break;
+    case B200_KEY_U32: LAUNCH_PART(B200_KEY_U32); break;
+    case B200_KEY_F32: LAUNCH_PART(B200_KEY_F32); break;
+    default: B200_REQUIRE(false, "sort_mgpu: 32-bit key types only (got %d)", key_type);
+  }
+#undef LAUNCH_PART
+  B200_LAUNCH_OK();
+  return 0;
+}
+
+// Offsets of workspace fields, so Python can read them without mirroring the struct.
+extern "C" size_t b200_symm_offset(const char* field) {
+  if (!strcmp(field, "error")) return offsetof(SymmWorkspace, error);
+  if (!strcmp(field, "sort_cursor")) return offsetof(SymmWorkspace, sort_cursor);
+  if (!strcmp(field, "sort_splitters")) return offsetof(SymmWorkspace, sort_splitters);
+  if (!strcmp(field, "sort_recv_count")) return offsetof(SymmWorkspace, sort_recv_count);
+  if (!strcmp(field, "sort_samples")) return offsetof(SymmWorkspace, sort_samples);
+  if (!strcmp(field, "flags")) return offsetof(SymmWorkspace, flags);
+  return (size_t)-1;
+}

@@ -1,0 +1,257 @@
+"""The lab workloads sharded over the ranks of a PeerGroup.
+
+======================  ===================================  ===========================
+workload                fused (product)                      nccl (baseline)
+======================  ===================================  ===========================
+``ShardedRoberts``      stencil kernel loads the halo row    isend/irecv of the halo row,
+(row bands)             from the next GPU's band in place    then the same kernel
+``ShardedClassifier``   statistics kernel all-reduces the    moments kernel, NCCL
+(row bands)             integer moments over peer memory     all_reduce, finalize kernel
+``ShardedSort``         partition kernel stores keys into    local partition, counts +
+(key shards)            the destination GPUs' buckets        keys by NCCL all_to_all
+======================  ===================================  ===========================
+(The reference has no multi-GPU code; both columns are new.  See csrc/mgpu_*.cu.)
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import List, Optional, Sequence, Tuple
+
+import numpy as np
+import torch
+
+from .. import _native as N
+from ..ops import classify as CL
+from ..ops import roberts as RB
+from ..ops import sort as ST
+from .symm import PeerGroup, SymmetricBuffer
+
+N.register("b200_lab3_stats_allreduce", C.c_int,
+           [C.c_void_p, C.c_int, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p,
+            C.c_int, C.c_int, C.c_uint64, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p])
+N.register("b200_sort_mgpu_splitters", C.c_int,
+           [C.c_void_p, C.c_size_t, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_uint64, C.c_int,
+            C.c_void_p])
+N.register("b200_sort_mgpu_scatter", C.c_int,
+           [C.c_void_p, C.c_size_t, C.c_int, C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p),
+            C.c_size_t, C.c_void_p, C.POINTER(C.c_void_p), C.c_int, C.c_int, C.c_uint64, C.c_int,
+            C.c_void_p])
+N.register("b200_sort_devn", C.c_int,
+           [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_int, C.c_void_p, C.c_size_t, C.c_void_p])
+N.register("b200_sort_ex", C.c_int,
+           [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_int, C.c_void_p, C.c_size_t,
+            C.c_void_p])
+
+
+def shard_rows(h: int, world: int) -> List[Tuple[int, int]]:
+    """Contiguous, near-equal row bands [(y0, y1)] — every band non-empty when h >= world."""
+    base, extra = divmod(h, world)
+    out, y = [], 0
+    for r in range(world):
+        n = base + (1 if r < extra else 0)
+        out.append((y, y + n))
+        y += n
+    return out
+
+
+def _ptr_array(values: Sequence[int]):
+    arr = (C.c_void_p * len(values))()
+    for i, v in enumerate(values):
+        arr[i] = v
+    return arr
+
+
+# ------------------------------------------------------------------------- lab2
+class ShardedRoberts:
+    """Row-sharded Roberts filter.  The band lives in a symmetric buffer so that rank
+    r-1's kernel can read this band's first row as its halo."""
+
+    def __init__(self, group: PeerGroup, w: int, h_total: int, impl: str = "fused", variant: str = "auto"):
+        assert impl in ("fused", "nccl")
+        self.group, self.w, self.h_total, self.impl, self.variant = group, w, h_total, impl, variant
+        self.y0, self.y1 = shard_rows(h_total, group.world)[group.rank]
+        self.h_local = self.y1 - self.y0
+        self.sym_in: SymmetricBuffer = group.alloc(max(1, self.h_local) * w * 4)
+        self.band = self.sym_in.view(torch.int32, self.h_local, w)
+        self.out = torch.empty((self.h_local, w), dtype=torch.int32, device=group.device)
+        self.halo = torch.empty(w, dtype=torch.int32, device=group.device) if impl == "nccl" else None
+        self.launches_per_step = 1
+
+    def below_address(self) -> Optional[int]:
+        r = self.group.rank
+        return None if r == self.group.world - 1 else self.sym_in.peer_address(r + 1)
+
+    def step(self) -> torch.Tensor:
+        g = self.group
+        if self.impl == "fused":
+            below = self.below_address()
+        else:
+            dist = g.dist
+            ops = []
+            if g.rank > 0:
+                ops.append(dist.P2POp(dist.isend, self.band[0], g.rank - 1, group=g.pg))
+            if g.rank < g.world - 1:
+                ops.append(dist.P2POp(dist.irecv, self.halo, g.rank + 1, group=g.pg))
+            if ops:
+                for req in dist.batch_isend_irecv(ops):
+                    req.wait()
+            below = self.halo if g.rank < g.world - 1 else None
+        return RB.roberts(self.band, self.out, below_row=below, variant=self.variant)
+
+
+# ------------------------------------------------------------------------- lab3
+def fused_stats(img: torch.Tensor, w: int, y0: int, h_local: int, d_pts: torch.Tensor, d_off: torch.Tensor,
+                nc: int, ws_ptrs_dev: torch.Tensor, rank: int, world: int, epoch: int,
+                params: torch.Tensor, moments_out: Optional[torch.Tensor], phase_mask: int = 3) -> None:
+    N.check(N.lib().b200_lab3_stats_allreduce(
+        N.ptr(img), w, y0, h_local, N.ptr(d_pts), N.ptr(d_off), nc, N.ptr(ws_ptrs_dev), rank, world,
+        epoch, N.ptr(params), N.ptr(moments_out), phase_mask, N.current_stream_ptr()),
+        "b200_lab3_stats_allreduce")
+
+
+class ShardedClassifier:
+    """Row-sharded lab3: global sample points, statistics all-reduced, local classify."""
+
+    def __init__(self, group: PeerGroup, w: int, h_total: int, classes, impl: str = "fused",
+                 variant: str = "auto"):
+        assert impl in ("fused", "nccl")
+        self.group, self.w, self.h_total, self.impl, self.variant = group, w, h_total, impl, variant
+        self.y0, self.y1 = shard_rows(h_total, group.world)[group.rank]
+        self.h_local = self.y1 - self.y0
+        self.nc = len(classes)
+        pts, off = CL.pack_points(classes)
+        dev = group.device
+        self.d_pts = torch.from_numpy(pts).to(dev) if pts.size else torch.zeros(2, dtype=torch.int32, device=dev)
+        self.d_off = torch.from_numpy(off).to(dev)
+        self.band = torch.empty((self.h_local, w), dtype=torch.int32, device=dev)
+        self.params = torch.empty((self.nc, CL.N_PARAMS), dtype=torch.float64, device=dev)
+        self.moments = torch.zeros((self.nc, CL.N_MOMENTS), dtype=torch.int64, device=dev)
+        npix = self.h_local * w
+        need = N.lib().b200_lab3_classify_scratch_bytes(npix, CL.CLASSIFY_VARIANTS[variant])
+        self.scratch = torch.empty(need, dtype=torch.uint8, device=dev) if need else None
+        self.ws = group.workspace()
+        lut = need > 0
+        # kernels per step: stats(1) [+ finalize for nccl] + classify (lut: build + apply)
+        self.launches_per_step = (1 if impl == "fused" else 2) + (2 if lut else 1)
+
+    def fit(self) -> torch.Tensor:
+        g = self.group
+        if self.impl == "fused":
+            fused_stats(self.band, self.w, self.y0, self.h_local, self.d_pts, self.d_off, self.nc,
+                        self.ws.ptrs_dev, g.rank, g.world, g.next_epoch(), self.params, self.moments, 3)
+        else:
+            self.moments.zero_()
+            CL.lab3_moments(self.band, self.d_pts, self.d_off, self.nc, self.moments, y0=self.y0)
+            g.dist.all_reduce(self.moments, op=g.dist.ReduceOp.SUM, group=g.pg)
+            CL.lab3_finalize(self.moments, self.params)
+        return self.params
+
+    def step(self) -> torch.Tensor:
+        self.fit()
+        return CL.lab3_classify(self.band, self.params, variant=self.variant, scratch=self.scratch)
+
+
+# ------------------------------------------------------------------------- lab5
+def mgpu_splitters(keys: torch.Tensor, samples_per_rank: int, ws_ptrs_dev: torch.Tensor, rank: int,
+                   world: int, epoch: int, phase_mask: int = 3) -> None:
+    N.check(N.lib().b200_sort_mgpu_splitters(
+        N.ptr(keys), keys.numel(), ST.KEY_TYPES[keys.dtype], samples_per_rank, N.ptr(ws_ptrs_dev), rank,
+        world, epoch, phase_mask, N.current_stream_ptr()), "b200_sort_mgpu_splitters")
+
+
+def mgpu_scatter(keys: torch.Tensor, splitters_addr: int, bucket_ptrs: Sequence[int],
+                 cursor_ptrs: Optional[Sequence[int]], capacity: int, ws: SymmetricBuffer, rank: int,
+                 world: int, epoch: int, phase_mask: int = 3) -> None:
+    N.check(N.lib().b200_sort_mgpu_scatter(
+        N.ptr(keys), keys.numel(), ST.KEY_TYPES[keys.dtype], C.c_void_p(splitters_addr),
+        _ptr_array(bucket_ptrs), _ptr_array(cursor_ptrs) if cursor_ptrs is not None else None, capacity,
+        N.ptr(ws.ptrs_dev), _ptr_array(ws.peer_ptrs), rank, world, epoch, phase_mask,
+        N.current_stream_ptr()), "b200_sort_mgpu_scatter")
+
+
+def sort_devn(bucket: torch.Tensor, tmp: torch.Tensor, count_addr: int, scratch: torch.Tensor) -> None:
+    N.check(N.lib().b200_sort_devn(N.ptr(bucket), N.ptr(tmp), bucket.numel(), C.c_void_p(count_addr),
+                                   ST.KEY_TYPES[bucket.dtype], N.ptr(scratch), scratch.numel(),
+                                   N.current_stream_ptr()), "b200_sort_devn")
+
+
+def samples_per_rank_for(world: int) -> int:
+    return 8192 // world if world & (world - 1) == 0 else 1 << int(np.log2(8192 // world))
+
+
+class ShardedSort:
+    """Sample sort over the ranks.  After ``step()`` rank r holds the r-th slice of the
+    globally sorted sequence in ``bucket[:count()]``."""
+
+    SLACK = 1.25
+
+    def __init__(self, group: PeerGroup, n_local: int, dtype: torch.dtype = torch.int32, impl: str = "fused"):
+        assert impl in ("fused", "nccl")
+        if group.world & (group.world - 1):
+            raise ValueError("ShardedSort needs a power-of-two number of ranks")
+        self.group, self.n_local, self.dtype, self.impl = group, n_local, dtype, impl
+        dev, world = group.device, group.world
+        self.keys = torch.empty(n_local, dtype=dtype, device=dev)
+        self.capacity = n_local if world == 1 else int(n_local * self.SLACK) + 8192
+        self.sym_bucket = group.alloc(self.capacity * 4)
+        self.bucket = self.sym_bucket.view(dtype, self.capacity)
+        self.tmp = torch.empty(self.capacity, dtype=dtype, device=dev)
+        self.scratch = torch.empty(ST.sort_scratch_bytes(self.capacity, dtype), dtype=torch.uint8, device=dev)
+        self.ws = group.workspace()
+        self.samples = samples_per_rank_for(world)
+        self._off = {k: group.ws_offset(k) for k in ("sort_splitters", "sort_recv_count", "sort_cursor")}
+        if impl == "nccl" and world > 1:
+            self.send = torch.empty((world, n_local), dtype=dtype, device=dev)
+            self.cursors = torch.zeros(world, dtype=torch.int64, device=dev)
+            self.count_dev = torch.zeros(1, dtype=torch.int64, device=dev)
+        # kernels per step: splitters + scatter + memset-free sort (hist, scan, 4 passes)
+        self.launches_per_step = (6 if world == 1 else 8)
+        self._count_host: Optional[int] = None
+
+    def step(self) -> None:
+        g, world, r = self.group, self.group.world, self.group.rank
+        self._count_host = None
+        if world == 1:
+            # out of place: pass 0 reads `keys`, the result lands in `bucket`
+            N.check(N.lib().b200_sort_ex(N.ptr(self.keys), N.ptr(self.bucket), N.ptr(self.tmp), self.n_local,
+                                         None, ST.KEY_TYPES[self.dtype], N.ptr(self.scratch),
+                                         self.scratch.numel(), N.current_stream_ptr()), "b200_sort_ex")
+            self._count_host = self.n_local
+            return
+        ws_local = self.ws.local_ptr
+        mgpu_splitters(self.keys, self.samples, self.ws.ptrs_dev, r, world, g.next_epoch(), 3)
+        if self.impl == "fused":
+            mgpu_scatter(self.keys, ws_local + self._off["sort_splitters"], self.sym_bucket.peer_ptrs, None,
+                         self.capacity, self.ws, r, world, g.next_epoch(), 3)
+            sort_devn(self.bucket, self.tmp, ws_local + self._off["sort_recv_count"], self.scratch)
+            return
+        # ---- NCCL baseline: partition into local send segments, exchange with all_to_all
+        dist = g.dist
+        self.cursors.zero_()
+        seg = [self.send[d].data_ptr() for d in range(world)]
+        cur = [self.cursors[d:].data_ptr() for d in range(world)]
+        mgpu_scatter(self.keys, ws_local + self._off["sort_splitters"], seg, cur, self.n_local, self.ws, r,
+                     world, g.next_epoch(), 1 | 4)
+        recv_counts = torch.empty_like(self.cursors)
+        dist.all_to_all_single(recv_counts, self.cursors, group=g.pg)
+        send_n, recv_n = self.cursors.tolist(), recv_counts.tolist()
+        total = int(sum(recv_n))
+        if total > self.capacity:
+            raise RuntimeError(f"rank {r}: bucket overflow ({total} > {self.capacity})")
+        outs, o = [], 0
+        for d in range(world):
+            outs.append(self.bucket[o: o + recv_n[d]])
+            o += recv_n[d]
+        ins = [self.send[d, : send_n[d]] for d in range(world)]
+        dist.all_to_all(outs, ins, group=g.pg)
+        ST.sort_(self.bucket[:total], self.tmp[:total], self.scratch)
+        self._count_host = total
+
+    def count(self) -> int:
+        if self._count_host is None:
+            off = self._off["sort_recv_count"]
+            self._count_host = int(self.ws.local[off: off + 8].view(torch.int64).item())
+        return self._count_host
+
+    def result(self) -> torch.Tensor:
+        return self.bucket[: self.count()]

@@ -104,6 +104,63 @@ size_t b200_sort_scratch_bytes(size_t n, int key_type);
 int b200_sort(void* keys, void* tmp, size_t n, int key_type, void* scratch,
               size_t scratch_bytes, b200_stream_t s);
 
+/* As b200_sort, with two options: `input` (may be NULL) is read by the first pass
+ * instead of `keys` and left untouched (out-of-place sort without a copy); `n_dev`
+ * (may be NULL) points to the actual length on the device, n then being only the
+ * upper bound that sizes grids and scratch (the multi-GPU bucket's fill count). */
+int b200_sort_ex(const void* input, void* keys, void* tmp, size_t n,
+                 const unsigned long long* n_dev, int key_type, void* scratch,
+                 size_t scratch_bytes, b200_stream_t s);
+int b200_sort_devn(void* keys, void* tmp, size_t n, const unsigned long long* n_dev,
+                   int key_type, void* scratch, size_t scratch_bytes, b200_stream_t s);
+
+/* ------------------------------------------------- peer memory / multi-GPU */
+/* One process per GPU.  Buffers are cudaMalloc'ed here, exported as 64-byte CUDA
+ * IPC handles, exchanged by the caller (torch.distributed) and opened on every
+ * peer; kernels then dereference the mapped peer addresses over NVLink.
+ * (The reference has no multi-GPU code: everything in this section is new.) */
+int b200_dev_malloc(void** p, size_t bytes); /* zero-filled */
+int b200_dev_free(void* p);
+int b200_ipc_export(void* p, void* handle64);
+int b200_ipc_open(const void* handle64, void** p);
+int b200_ipc_close(void* p);
+int b200_peer_can_access(int dev, int peer);
+int b200_enable_peer_access(int peer);
+/* size of the per-rank symmetric workspace (flags, lab3 slots, sort samples/cursor)
+ * and byte offsets of its fields ("error", "sort_cursor", "sort_splitters",
+ * "sort_recv_count", "sort_samples", "flags"). */
+size_t b200_symm_workspace_bytes(void);
+size_t b200_symm_offset(const char* field);
+/* Stream-ordered barrier over peer memory: signal every rank, wait for every rank.
+ * ws_ptrs: device array [world] of the ranks' workspace addresses; epoch grows by
+ * one per call, identically on all ranks. */
+int b200_symm_barrier(const void* ws_ptrs, int rank, int world, uint64_t epoch,
+                      b200_stream_t s);
+
+/* lab3 fused: class moments of this rank's band, all-reduced across ranks inside
+ * the kernel (remote stores into the peers' slots + system-scope flags), then mean
+ * and inverse covariance.  phase_mask 3 = whole thing (product path); 1 / 2 run the
+ * push and the wait+reduce halves separately (single-GPU testing of virtual ranks). */
+int b200_lab3_stats_allreduce(const void* img, int w, int64_t y0, int64_t h_local,
+                              const int* pts, const int* class_off, int nc,
+                              const void* ws_ptrs, int rank, int world, uint64_t epoch,
+                              double* params, long long* moments_out, int phase_mask,
+                              b200_stream_t s);
+
+/* lab5 fused sample sort, step 1: sample + exchange + splitters (one CTA). */
+int b200_sort_mgpu_splitters(const void* keys, size_t n_local, int key_type,
+                             int samples_per_rank, const void* ws_ptrs, int rank, int world,
+                             uint64_t epoch, int phase_mask, b200_stream_t s);
+/* step 2: partition fused with the all-to-all — keys are stored straight into the
+ * destination ranks' buckets (bucket_ptrs: HOST array [world] of peer-mapped device
+ * addresses), space reserved with one remote atomic per tile and destination.
+ * phase_mask: 1 scatter+signal, 2 wait+publish count, 4 (with 1) local only. */
+int b200_sort_mgpu_scatter(const void* keys, size_t n_local, int key_type,
+                           const void* splitters, void* const* bucket_ptrs,
+                           void* const* cursor_ptrs, size_t capacity, const void* ws_ptrs,
+                           void* const* ws_host_ptrs, int rank, int world, uint64_t epoch,
+                           int phase_mask, b200_stream_t s);
+
 /* ------------------------------------------------------------- CPU oracles */
 /* Plain C++ restatements used by the tests and the CPU binaries. */
 void b200_cpu_vecsub_f64(const double* a, const double* b, double* c, size_t n);

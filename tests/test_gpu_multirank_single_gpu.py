@@ -1,0 +1,121 @@
+"""The multi-rank kernels exercised on ONE GPU: `world` virtual ranks live in one
+process, their "peer" pointers are each other's buffers, and the kernels run phase
+by phase (push/signal for every rank first, wait/reduce afterwards) so that no
+kernel ever waits on another launch."""
+import numpy as np
+import pytest
+import torch
+
+from cuda_mpi_openmp_b200 import ops
+from cuda_mpi_openmp_b200.models import MahalanobisClassifier, RobertsFilter
+from cuda_mpi_openmp_b200.parallel import LocalPeerGroup, shard_rows
+from cuda_mpi_openmp_b200.parallel import sharded as S
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+@pytest.mark.parametrize("variant", ["tma", "stream"])
+def test_roberts_bands_in_symmetric_buffers(cuda_device, world, variant):
+    rng = np.random.default_rng(world)
+    h, w = 1000 + world, 768
+    img = rng.integers(0, 256, size=(h, w, 4), dtype=np.uint8)
+    group = LocalPeerGroup(world, cuda_device)
+    bands = shard_rows(h, world)
+    bufs = group.alloc(max(b - a for a, b in bands) * w * 4)
+    for r, (a, b) in enumerate(bands):
+        bufs[r].view(torch.uint8, b - a, w, 4).copy_(torch.from_numpy(img[a:b]))
+    outs = []
+    for r, (a, b) in enumerate(bands):
+        below = bufs[r].peer_address(r + 1) if r + 1 < world else None   # "peer" pointer, raw address
+        band = bufs[r].view(torch.int32, b - a, w)
+        outs.append(ops.roberts(band, below_row=below, variant=variant).cpu().numpy())
+    got = np.concatenate(outs, axis=0).view(np.uint8).reshape(h, w, 4)
+    assert np.array_equal(got, RobertsFilter.reference(img))
+    for b in bufs:
+        b.free()
+
+
+@pytest.mark.parametrize("world", [1, 2, 8])
+def test_lab3_stats_allreduce_matches_single_gpu_bitwise(cuda_device, world):
+    rng = np.random.default_rng(40 + world)
+    h, w, nc = 257, 300, 32
+    img = rng.integers(0, 256, size=(h, w, 4), dtype=np.uint8)
+    classes = [np.stack([rng.integers(0, w, 3000), rng.integers(0, h, 3000)], axis=1) for _ in range(nc)]
+    want = MahalanobisClassifier.reference_params(img, classes, mode="moments")
+    pts, off = ops.classify.pack_points(classes)
+    d_pts, d_off = torch.from_numpy(pts).to(cuda_device), torch.from_numpy(off).to(cuda_device)
+    group = LocalPeerGroup(world, cuda_device)
+    ws = group.workspaces()
+    bands = shard_rows(h, world)
+    d_bands = [torch.from_numpy(img[a:b].copy()).to(cuda_device) for a, b in bands]
+    params = [torch.zeros((nc, 12), dtype=torch.float64, device=cuda_device) for _ in range(world)]
+    for rep in range(3):                      # epochs alternate the slot parity
+        epoch = group.next_epoch()
+        for r, (a, b) in enumerate(bands):    # phase 1 on every rank: accumulate, push, signal
+            S.fused_stats(d_bands[r], w, a, b - a, d_pts, d_off, nc, ws[r].ptrs_dev, r, world, epoch, params[r], None, 1)
+        for r, (a, b) in enumerate(bands):    # phase 2: wait (already satisfied), reduce, finalize
+            S.fused_stats(d_bands[r], w, a, b - a, d_pts, d_off, nc, ws[r].ptrs_dev, r, world, epoch, params[r], None, 2)
+        for r in range(world):
+            assert np.array_equal(params[r].cpu().numpy().view(np.int64), want.view(np.int64)), (rep, r)
+    assert all(int(w_.local[group.ranks[0].ws_offset("error"):][:8].view(torch.int64).item()) == 0 for w_ in ws)
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+@pytest.mark.parametrize("dtype,kind", [(np.int32, "random"), (np.float32, "random"), (np.int32, "dups"),
+                                        (np.int32, "equal"), (np.uint32, "skewed")])
+def test_sample_sort_fused_scatter(cuda_device, world, dtype, kind):
+    rng = np.random.default_rng(50 + world)
+    n_local = 100_000 + 37
+    shards = []
+    for r in range(world):
+        if dtype == np.float32:
+            k = (rng.standard_normal(n_local) * 1e3).astype(np.float32)
+        else:
+            info = np.iinfo(dtype)
+            k = rng.integers(info.min, info.max, n_local, dtype=np.int64, endpoint=True).astype(dtype)
+        if kind == "dups":
+            k = k[rng.integers(0, 5, n_local)]
+        elif kind == "equal":
+            k[:] = 7
+        elif kind == "skewed":                 # every rank holds a different key range
+            k = (k // world + r * (info.max // world)).astype(dtype)
+        shards.append(k)
+    tdt = {np.int32: torch.int32, np.float32: torch.float32, np.uint32: torch.uint32}[dtype]
+    group = LocalPeerGroup(world, cuda_device)
+    ws = group.workspaces()
+    capacity = int(n_local * 1.25) + 8192
+    buckets = group.alloc(capacity * 4)
+    d_keys = [torch.from_numpy(s.copy()).to(cuda_device) for s in shards]
+    spr = S.samples_per_rank_for(world)
+    off = {k: group.ranks[0].ws_offset(k) for k in ("sort_splitters", "sort_recv_count", "error")}
+    e1, e2 = group.next_epoch(), group.next_epoch()
+    for r in range(world):
+        S.mgpu_splitters(d_keys[r], spr, ws[r].ptrs_dev, r, world, e1, 1)
+    for r in range(world):
+        S.mgpu_splitters(d_keys[r], spr, ws[r].ptrs_dev, r, world, e1, 2)
+    split0 = ws[0].local[off["sort_splitters"]:][: 8 * world].view(torch.int64).cpu()
+    for r in range(1, world):               # every rank derived the same splitters
+        assert torch.equal(ws[r].local[off["sort_splitters"]:][: 8 * world].view(torch.int64).cpu(), split0)
+    for r in range(world):
+        S.mgpu_scatter(d_keys[r], ws[r].local_ptr + off["sort_splitters"], buckets[r].peer_ptrs, None, capacity,
+                       ws[r], r, world, e2, 1)
+    for r in range(world):
+        S.mgpu_scatter(d_keys[r], ws[r].local_ptr + off["sort_splitters"], buckets[r].peer_ptrs, None, capacity,
+                       ws[r], r, world, e2, 2)
+    parts, counts = [], []
+    for r in range(world):
+        bucket = buckets[r].view(tdt, capacity)
+        tmp = torch.empty_like(bucket)
+        scratch = torch.empty(ops.sort_scratch_bytes(capacity, tdt), dtype=torch.uint8, device=cuda_device)
+        S.sort_devn(bucket, tmp, ws[r].local_ptr + off["sort_recv_count"], scratch)
+        cnt = int(ws[r].local[off["sort_recv_count"]:][:8].view(torch.int64).item())
+        assert int(ws[r].local[off["error"]:][:8].view(torch.int64).item()) == 0
+        counts.append(cnt)
+        parts.append(bucket[:cnt].cpu().numpy())
+    assert sum(counts) == world * n_local
+    assert max(counts) <= capacity and max(counts) < 1.15 * n_local + 8192     # balanced, duplicates included
+    got = np.concatenate(parts)
+    assert np.array_equal(got, np.sort(np.concatenate(shards)))
+    for b in buckets:
+        b.free()
