@@ -158,6 +158,8 @@ def run_own(args):
                "matches_device_path": check}
         del host_in, host_out, pipe
     flag_out_sample = model.out[:2, :8].cpu().tolist()
+    group.barrier()
+    model.free()
     del model
     torch.cuda.empty_cache()
 
@@ -189,6 +191,7 @@ def run_own(args):
                                               "stats": "in-kernel all-reduce" if args.exchange == "fused" else "nccl"}
         t = timed_steps(group, m3.fit, 20, 3)
         labs["lab3_stats_allreduce_32x4096pts"] = {"ms": round(t, 4)}
+        group.barrier()
         del m3
         torch.cuda.empty_cache()
         # lab5: 2^31 32-bit keys over the ranks (sample sort, fused all-to-all)
@@ -199,6 +202,8 @@ def run_own(args):
         err = group.ws_error() if world > 1 else 0
         labs["lab5_sort_2^31_int32"] = {"ms": round(t, 3), "Gkeys_per_s": round(n_total / t / 1e6, 2),
                                         "bucket_keys_rank0": m5.count(), "error_word": err}
+        group.barrier()
+        m5.free()
         del m5
         torch.cuda.empty_cache()
 
@@ -282,7 +287,12 @@ def run_reference(args):
 
     try:
         barrier()
-        k0, wall0 = one_step()                        # first warm-up step doubles as a cost probe
+        try:
+            k0, wall0 = one_step()                    # first warm-up step doubles as a cost probe
+        except Exception as exc:  # noqa: BLE001 - e.g. no GPU on this box
+            if rank == 0:
+                print(json.dumps({"impl": "reference", "unavailable": " ".join(str(exc).split())[:300]}))
+            return
         budget_steps = max(1, int(args.ref_max_seconds * 1e3 / max(wall0, 1.0)) - 1)
         warmup = max(1, min(args.warmup, max(1, budget_steps // 4)))
         steps = max(1, min(args.steps, budget_steps - warmup + 1))

@@ -4,41 +4,47 @@
 // B200 design: pure HBM stream, 24 B/element.  Each thread moves 256-bit
 // vectors (ld.global.nc.v4.f64, new on sm_100) with four independent vector
 // pairs in flight before the first use, no L1 allocation on the way in and
-// evict-first on the way out.  Grid = SMs x resident CTAs (one wave, grid-stride).
+// evict-first on the way out.  One CTA per 32 KB slab, balanced by the hardware.
 #include "common.cuh"
 
 namespace b200 {
 
 constexpr int kVsThreads = 256;
 constexpr int kVsUnroll = 4;  // 4 x 32 B per array per thread in flight
+constexpr int kVsPerBlock = kVsThreads * kVsUnroll;  // 1024 vectors = 32 KB per array
 
+// One CTA per 32 KB slab of each array, no loop: every thread issues its eight
+// 256-bit loads back to back, then subtracts and stores.  The hardware CTA
+// scheduler balances the slabs over the SMs (no serialised grid-stride tail).
 __global__ void __launch_bounds__(kVsThreads)
     vecsub_v4_kernel(const double* __restrict__ a, const double* __restrict__ b,
                      double* __restrict__ c, size_t n_vec4) {
-  const size_t stride = (size_t)gridDim.x * kVsThreads;
-  size_t i = (size_t)blockIdx.x * kVsThreads + threadIdx.x;
-  // main loop: kVsUnroll vectors per thread per trip, all loads issued first
-  for (; i + (kVsUnroll - 1) * stride < n_vec4; i += kVsUnroll * stride) {
-    double va[kVsUnroll][4], vb[kVsUnroll][4];
+  const size_t base = (size_t)blockIdx.x * kVsPerBlock + threadIdx.x;
+  double va[kVsUnroll][4], vb[kVsUnroll][4];
+  if (base + (kVsUnroll - 1) * kVsThreads < n_vec4) {  // full slab (all but the last CTA)
 #pragma unroll
     for (int u = 0; u < kVsUnroll; ++u) {
-      ld_stream_f64x4(a + 4 * (i + u * stride), va[u]);
-      ld_stream_f64x4(b + 4 * (i + u * stride), vb[u]);
+      ld_stream_f64x4(a + 4 * (base + u * kVsThreads), va[u]);
+      ld_stream_f64x4(b + 4 * (base + u * kVsThreads), vb[u]);
     }
 #pragma unroll
     for (int u = 0; u < kVsUnroll; ++u) {
 #pragma unroll
       for (int k = 0; k < 4; ++k) va[u][k] = va[u][k] - vb[u][k];
-      st_stream_f64x4(c + 4 * (i + u * stride), va[u]);
+      st_stream_f64x4(c + 4 * (base + u * kVsThreads), va[u]);
     }
-  }
-  for (; i < n_vec4; i += stride) {
-    double va[4], vb[4];
-    ld_stream_f64x4(a + 4 * i, va);
-    ld_stream_f64x4(b + 4 * i, vb);
+  } else {
 #pragma unroll
-    for (int k = 0; k < 4; ++k) va[k] = va[k] - vb[k];
-    st_stream_f64x4(c + 4 * i, va);
+    for (int u = 0; u < kVsUnroll; ++u) {
+      const size_t i = base + u * kVsThreads;
+      if (i < n_vec4) {
+        ld_stream_f64x4(a + 4 * i, va[u]);
+        ld_stream_f64x4(b + 4 * i, vb[u]);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) va[u][k] = va[u][k] - vb[u][k];
+        st_stream_f64x4(c + 4 * i, va[u]);
+      }
+    }
   }
 }
 
@@ -63,9 +69,8 @@ extern "C" int b200_vecsub_f64(const double* a, const double* b, double* c, size
   size_t n_vec4 = aligned ? n / 4 : 0;
   const int sms = device_info().sm_count;
   if (n_vec4) {
-    size_t want = (n_vec4 + kVsThreads - 1) / kVsThreads;
-    int grid = (int)(want < (size_t)sms * 8 ? want : (size_t)sms * 8);
-    vecsub_v4_kernel<<<grid, kVsThreads, 0, st>>>(a, b, c, n_vec4);
+    const size_t grid = (n_vec4 + kVsPerBlock - 1) / kVsPerBlock;
+    vecsub_v4_kernel<<<(unsigned)grid, kVsThreads, 0, st>>>(a, b, c, n_vec4);
     B200_LAUNCH_OK();
   }
   size_t done = n_vec4 * 4;

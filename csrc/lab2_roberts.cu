@@ -8,10 +8,10 @@
 //    by shuffle.  Every input byte is loaded once and its luminance is computed
 //    once (the reference computes it four times); rows are prefetched U deep so
 //    each warp keeps U x 512 B in flight.
-//  * TMA     — persistent CTAs, mbarrier ring of TMA tile loads, output staged in
-//    shared memory and written back with TMA stores; CTA pairs in a cluster hand
-//    the strip-edge luminance column to each other through DSMEM
-//    (lab2_roberts_tma.cu).
+//  * TMA     — persistent CTAs, mbarrier ring of self-contained TMA tile loads
+//    (tile + its one-row / one-column stencil apron in a single box), output
+//    staged in shared memory and written back with per-warp TMA stores
+//    (lab2_roberts_tma.cu).  Fastest on large images: the AUTO choice.
 //  * GENERIC — one pixel per thread, any width/alignment, any launch geometry
 //    (the harness's block/grid sweep).
 // All variants take `below_row`: the row that follows the band.  For a row-
@@ -169,7 +169,12 @@ extern "C" int b200_roberts(const void* in, void* out, int w, int64_t h_local,
   RowSrc src = make_src(in, w, h_local, below_row);
   const bool vec_ok = stream_supported(in, out, src.below, w);
   if (variant == B200_ROBERTS_AUTO) {
-    variant = vec_ok ? B200_ROBERTS_STREAM : B200_ROBERTS_GENERIC;
+    // measured on B200 (profiles/): TMA 0.94 of the copy roofline on large images,
+    // STREAM 0.67; tiny images are launch-latency bound either way
+    if (roberts_tma_supported(in, out, w, h_local) && (int64_t)w * h_local >= (1 << 16))
+      variant = B200_ROBERTS_TMA;
+    else
+      variant = vec_ok ? B200_ROBERTS_STREAM : B200_ROBERTS_GENERIC;
   }
   switch (variant) {
     case B200_ROBERTS_STREAM:

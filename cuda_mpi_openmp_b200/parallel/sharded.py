@@ -22,8 +22,8 @@ import torch
 
 from .. import _native as N
 from ..ops import classify as CL
-from ..ops import roberts as RB
 from ..ops import sort as ST
+from ..ops.roberts import roberts as roberts_op
 from .symm import PeerGroup, SymmetricBuffer
 
 N.register("b200_lab3_stats_allreduce", C.c_int,
@@ -77,6 +77,11 @@ class ShardedRoberts:
         self.halo = torch.empty(w, dtype=torch.int32, device=group.device) if impl == "nccl" else None
         self.launches_per_step = 1
 
+    def free(self) -> None:
+        """Release the symmetric band (call on every rank, after a barrier)."""
+        self.band = None
+        self.sym_in.free()
+
     def below_address(self) -> Optional[int]:
         r = self.group.rank
         return None if r == self.group.world - 1 else self.sym_in.peer_address(r + 1)
@@ -96,7 +101,7 @@ class ShardedRoberts:
                 for req in dist.batch_isend_irecv(ops):
                     req.wait()
             below = self.halo if g.rank < g.world - 1 else None
-        return RB.roberts(self.band, self.out, below_row=below, variant=self.variant)
+        return roberts_op(self.band, self.out, below_row=below, variant=self.variant)
 
 
 # ------------------------------------------------------------------------- lab3
@@ -246,6 +251,10 @@ class ShardedSort:
         dist.all_to_all(outs, ins, group=g.pg)
         ST.sort_(self.bucket[:total], self.tmp[:total], self.scratch)
         self._count_host = total
+
+    def free(self) -> None:
+        self.bucket = None
+        self.sym_bucket.free()
 
     def count(self) -> int:
         if self._count_host is None:

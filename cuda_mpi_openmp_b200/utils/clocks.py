@@ -14,7 +14,7 @@ _REASONS = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_pow
 
 
 class ClockSampler:
-    def __init__(self, gpu_index: int = 0, period_ms: int = 200):
+    def __init__(self, gpu_index: int = 0, period_ms: int = 50):
         self.gpu_index, self.period_ms = gpu_index, period_ms
         self.rows: List[List[str]] = []
         self._proc = None

@@ -55,7 +55,7 @@ int b200_vecsub_f64_geom(const double* a, const double* b, double* c, size_t n,
 enum {
   B200_ROBERTS_AUTO = 0,
   B200_ROBERTS_STREAM = 1, /* register sliding window, 128-bit accesses      */
-  B200_ROBERTS_TMA = 2,    /* TMA tile pipeline + cluster/DSMEM column share */
+  B200_ROBERTS_TMA = 2,    /* persistent TMA tile pipeline, TMA stores          */
   B200_ROBERTS_GENERIC = 3 /* one pixel per thread, any alignment            */
 };
 int b200_roberts(const void* in, void* out, int w, int64_t h_local,

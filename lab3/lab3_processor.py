@@ -1,0 +1,2 @@
+"""Import shim: the processor lives in cuda_mpi_openmp_b200/harness/processors.py."""
+from cuda_mpi_openmp_b200.harness.processors import Lab3Processor  # noqa: F401
