@@ -412,3 +412,108 @@ extern "C" int b200_sort_ex(const void* input, void* keys, void* tmp, size_t n,
   }
   return 0;
 }
+
+// ------------------------------------------------------------- no-allocation sort
+// b200_sort_noalloc: the radix sort above for callers that must not allocate.
+//
+// b200_sort needs three pieces of device memory besides the keys: the digit
+// histograms, the tile tickets + look-back words, and a second key buffer to
+// ping-pong with.  Its callers obtain them with cudaMalloc (or from torch).  Some
+// callers cannot: a plug-in running inside a host application that has already
+// handed all device memory to its own pool, where a stray cudaMalloc fails or
+// starves the host; a latency-critical loop that cannot afford cudaMalloc /
+// cudaFree because both synchronise the whole device and stall every other
+// stream; code under a "no allocation after start-up" rule.  For them this entry
+// point keeps all of that memory in ONE file-scope device array that is part of
+// the library image: it exists on every GPU that loads the library, from load to
+// process exit, and costs B200_SORT_NOALLOC_SCRATCH_BYTES (about 4.3 MB) there.
+//
+//   * at most B200_SORT_NOALLOC_MAX_KEYS (2^20) keys per call; larger n is
+//     rejected with an error, nothing is launched;
+//   * `input` is only read, `output` receives the sorted keys (they may be the
+//     same buffer); the caller owns both;
+//   * the first call on each device looks up the array's device address with
+//     cudaGetSymbolAddress (the name is only a host-side handle in host code) and
+//     caches it; make that first call before starting any stream capture;
+//   * the array is shared by every call on that GPU and still holds the previous
+//     call's words, so each call zero-fills the part it relies on (histograms,
+//     tickets, look-back) on its stream before launching;
+//   * because the array is shared, two calls whose kernels can overlap on the
+//     same GPU (different streams, or different host threads) race on it: run
+//     them on one stream or order them with events.
+// Calls nothing that allocates: no cudaMalloc/cudaFree, no torch, no library
+// routine with a workspace.  (No counterpart in the reference.)
+#include <mutex>
+
+namespace b200 {
+
+constexpr size_t kNoAllocMaxKeys = B200_SORT_NOALLOC_MAX_KEYS;
+constexpr size_t kNoAllocBookBytes =
+    (4 * kRadix * sizeof(unsigned long long) + 64 +
+     ((kNoAllocMaxKeys + kTile - 1) / kTile) * kRadix * sizeof(unsigned long long) + 255) / 256 * 256;
+constexpr size_t kNoAllocBytes = kNoAllocBookBytes + kNoAllocMaxKeys * sizeof(uint32_t);
+static_assert(kNoAllocBytes == B200_SORT_NOALLOC_SCRATCH_BYTES, "header constant out of date");
+
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoAllocBytes];
+
+// Device address of g_noalloc_scratch on the CURRENT device, resolved once per device.
+static int noalloc_scratch(unsigned char** out) {
+  static std::mutex mu;
+  static unsigned char* cached[64] = {nullptr};
+  int dev = -1;
+  B200_CUDA_OK(cudaGetDevice(&dev));
+  B200_REQUIRE(dev >= 0 && dev < 64, "sort_noalloc: unexpected device ordinal %d", dev);
+  std::lock_guard<std::mutex> lock(mu);
+  if (!cached[dev]) {
+    void* p = nullptr;
+    B200_CUDA_OK(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+    B200_REQUIRE(p != nullptr, "sort_noalloc: scratch symbol has no device address");
+    cached[dev] = (unsigned char*)p;
+  }
+  *out = cached[dev];
+  return 0;
+}
+
+}  // namespace b200
+
+extern "C" int b200_sort_noalloc(const void* input, void* output, size_t n, int key_type,
+                                 b200_stream_t s) {
+  B200_REQUIRE(n <= kNoAllocMaxKeys,
+               "sort_noalloc: n = %zu exceeds the built-in scratch (at most %zu keys); use b200_sort "
+               "with caller-provided scratch for larger arrays",
+               n, (size_t)kNoAllocMaxKeys);
+  B200_REQUIRE(key_type == B200_KEY_I32 || key_type == B200_KEY_U32 || key_type == B200_KEY_F32 ||
+                   key_type == B200_KEY_U8,
+               "sort_noalloc: unknown key type %d", key_type);
+  if (n == 0) return 0;
+  B200_REQUIRE(input && output, "sort_noalloc: null key buffer");
+  unsigned char* base = nullptr;
+  if (int rc = noalloc_scratch(&base)) return rc;
+  cudaStream_t st = as_stream(s);
+  SortScratch sc = carve(base, n);  // histograms | tickets | look-back, then the key buffer
+  uint32_t* tmp = (uint32_t*)(base + kNoAllocBookBytes);
+  // the array still holds the previous call's counters and look-back states
+  B200_CUDA_OK(cudaMemsetAsync(base, 0, sc.bytes, st));
+  switch (key_type) {
+    case B200_KEY_I32:
+      return sort32<B200_KEY_I32>((const uint32_t*)input, (uint32_t*)output, tmp, n, nullptr, sc, st);
+    case B200_KEY_U32:
+      return sort32<B200_KEY_U32>((const uint32_t*)input, (uint32_t*)output, tmp, n, nullptr, sc, st);
+    case B200_KEY_F32:
+      return sort32<B200_KEY_F32>((const uint32_t*)input, (uint32_t*)output, tmp, n, nullptr, sc, st);
+    default: {  // B200_KEY_U8: histogram of the input, then the output is filled run by run
+      const int sms = device_info().sm_count;
+      size_t blocks = (n / 16 + kHistThreads - 1) / kHistThreads + 1;
+      if (blocks > (size_t)sms * 8) blocks = (size_t)sms * 8;
+      sort_u8_hist_kernel<<<(unsigned)blocks, kHistThreads, 0, st>>>((const uint8_t*)input, n, sc.hist);
+      B200_LAUNCH_OK();
+      sort_scan_kernel<<<1, kRadix, 0, st>>>(sc.hist, 1);
+      B200_LAUNCH_OK();
+      size_t fb = (n + 255) / 256;
+      if (fb > (size_t)sms * 16) fb = (size_t)sms * 16;
+      sort_u8_fill_kernel<<<(unsigned)fb, 256, 0, st>>>((uint8_t*)output, n, sc.hist);
+      B200_LAUNCH_OK();
+      return 0;
+    }
+  }
+}

@@ -114,6 +114,25 @@ int b200_sort_ex(const void* input, void* keys, void* tmp, size_t n,
 int b200_sort_devn(void* keys, void* tmp, size_t n, const unsigned long long* n_dev,
                    int key_type, void* scratch, size_t scratch_bytes, b200_stream_t s);
 
+/* Sort for callers that cannot allocate device memory (no counterpart in the
+ * reference).  Same result as b200_sort, but the histograms, tickets, look-back
+ * words and the second key buffer live in a device array built into the library
+ * (B200_SORT_NOALLOC_SCRATCH_BYTES on every GPU that loads it) instead of in
+ * caller-provided scratch.  Meant for code that runs where cudaMalloc is off
+ * limits: inside a host application whose own pool already owns the GPU's memory,
+ * in a latency-critical loop that cannot take cudaMalloc/cudaFree's device-wide
+ * synchronisation, or under a no-allocation-after-start-up rule.
+ *  - n must not exceed B200_SORT_NOALLOC_MAX_KEYS: larger n returns an error.
+ *  - input is read only; output receives the sorted keys; they may alias.
+ *  - the first call on a device resolves the array's address
+ *    (cudaGetSymbolAddress); issue it before any stream capture begins.
+ *  - all calls on a GPU share the array: calls that may overlap there (other
+ *    streams or threads) race — keep them on one stream or order them. */
+#define B200_SORT_NOALLOC_MAX_KEYS (1u << 20)
+#define B200_SORT_NOALLOC_SCRATCH_BYTES 4464896u
+int b200_sort_noalloc(const void* input, void* output, size_t n, int key_type,
+                      b200_stream_t s);
+
 /* ------------------------------------------------- peer memory / multi-GPU */
 /* One process per GPU.  Buffers are cudaMalloc'ed here, exported as 64-byte CUDA
  * IPC handles, exchanged by the caller (torch.distributed) and opened on every
