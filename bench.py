@@ -192,6 +192,7 @@ def run_own(args):
         t = timed_steps(group, m3.fit, 20, 3)
         labs["lab3_stats_allreduce_32x4096pts"] = {"ms": round(t, 4)}
         group.barrier()
+        m3.free()
         del m3
         torch.cuda.empty_cache()
         # lab5: 2^31 32-bit keys over the ranks (sample sort, fused all-to-all)

@@ -94,6 +94,22 @@ __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return (uint32_t)__cvta_generic_to_shared(p);
 }
 
+// Lanes of the warp whose `label` equals mine, from BITS ballots instead of
+// MATCH.ANY: on B200 the match instruction is issued at roughly one warp per ~60
+// cycles per SM (ADU pipe, measured with ncu: 60% of the radix-sort samples sat on
+// its result), while VOTE + LOP3 run at ALU rate.
+template <int BITS>
+__device__ __forceinline__ uint32_t match_any_bits(uint32_t label) {
+  uint32_t peers = 0xffffffffu;
+#pragma unroll
+  for (int b = 0; b < BITS; ++b) {
+    const bool bit = (label >> b) & 1u;
+    const uint32_t m = __ballot_sync(0xffffffffu, bit);
+    peers &= bit ? m : ~m;
+  }
+  return peers;
+}
+
 // ---- mbarrier / TMA -------------------------------------------------------
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
@@ -122,6 +138,21 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
 }
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   while (!mbar_try_wait(bar, parity)) {
+  }
+}
+// same, but lets the hardware keep the warp suspended for up to `hint_ns` per
+// probe, so waiting warps do not eat issue slots the computing warps need
+__device__ __forceinline__ void mbar_wait_relaxed(uint64_t* bar, uint32_t parity,
+                                                  uint32_t hint_ns = 2000) {
+  uint32_t ok = 0;
+  while (!ok) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(smem_u32(bar)), "r"(parity), "r"(hint_ns)
+        : "memory");
   }
 }
 // 2-D tiled TMA load global -> shared, completion counted on an mbarrier.

@@ -116,7 +116,7 @@ __global__ void __launch_bounds__(kTmaThreads, 1)
       if (lane == 31 && has_right) below_edge = ld_stream_u32(P.below + x + 4);
     }
 
-    mbar_wait(&full[s], ph);
+    mbar_wait_relaxed(&full[s], ph);
 
     uint4 px[kSubH + 1];
     uint32_t edge[kSubH + 1];

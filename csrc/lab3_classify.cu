@@ -21,9 +21,6 @@
 
 namespace b200 {
 
-constexpr int kNP = B200_LAB3_PARAMS;
-constexpr int kNM = B200_LAB3_MOMENTS;
-constexpr int kMaxC = B200_LAB3_MAX_CLASSES;
 
 // ------------------------------------------------------------------ statistics
 constexpr int kMomThreads = 256;
@@ -75,54 +72,7 @@ __global__ void lab3_finalize_kernel(const long long* __restrict__ moments, int 
 }
 
 // ------------------------------------------------------------------- classify
-// distance of colour (r,g,b) to one class: the reference's operation chain
-//   temp[i] = fma(d2,m[2][i], fma(d1,m[1][i], fma(d0,m[0][i], 0)))
-//   dist    = fma(d2,temp[2], fma(d1,temp[1], fma(d0,temp[0], 0)))
-__device__ __forceinline__ double maha(double r, double g, double b, const double* p) {
-  const double d0 = __dsub_rn(r, p[0]), d1 = __dsub_rn(g, p[1]), d2 = __dsub_rn(b, p[2]);
-  double t0 = __fma_rn(d0, p[3], 0.0), t1 = __fma_rn(d0, p[4], 0.0), t2 = __fma_rn(d0, p[5], 0.0);
-  t0 = __fma_rn(d1, p[6], t0), t1 = __fma_rn(d1, p[7], t1), t2 = __fma_rn(d1, p[8], t2);
-  t0 = __fma_rn(d2, p[9], t0), t1 = __fma_rn(d2, p[10], t1), t2 = __fma_rn(d2, p[11], t2);
-  double dist = __fma_rn(d0, t0, 0.0);
-  dist = __fma_rn(d1, t1, dist);
-  return __fma_rn(d2, t2, dist);
-}
-
-template <int NPX>
-__device__ __forceinline__ void classify_group(const uint32_t (&px)[NPX], int nc,
-                                               const double* sp, int (&best)[NPX]) {
-  double r[NPX], g[NPX], b[NPX], mind[NPX];
-#pragma unroll
-  for (int k = 0; k < NPX; ++k) {
-    r[k] = (double)(px[k] & 0xff);
-    g[k] = (double)((px[k] >> 8) & 0xff);
-    b[k] = (double)((px[k] >> 16) & 0xff);
-    mind[k] = DBL_MAX;
-    best[k] = -1;
-  }
-  for (int c = 0; c < nc; ++c) {
-    double p[kNP];
-#pragma unroll
-    for (int j = 0; j < kNP; ++j) p[j] = sp[c * kNP + j];
-#pragma unroll
-    for (int k = 0; k < NPX; ++k) {
-      const double d = maha(r[k], g[k], b[k], p);
-      if (d < mind[k]) {
-        mind[k] = d;
-        best[k] = c;
-      }
-    }
-  }
-}
-
-__device__ __forceinline__ uint32_t set_alpha(uint32_t px, int cls) {
-  return (px & 0x00ffffffu) | ((uint32_t)(cls & 0xff) << 24);
-}
-
-__device__ __forceinline__ void load_params_smem(double* sp, const double* params, int nc) {
-  for (int i = threadIdx.x; i < nc * kNP; i += blockDim.x) sp[i] = params[i];
-  __syncthreads();
-}
+// (maha / classify_group / set_alpha / load_params_smem live in lab3_math.cuh)
 
 constexpr int kClsThreads = 256;
 
@@ -297,5 +247,32 @@ extern "C" int b200_lab3_classify_geom(void* img, int64_t npix, int nc, const do
   lab3_classify_scalar_kernel<<<blocks, threads, 0, as_stream(s)>>>((uint32_t*)img, 0, npix, nc,
                                                                     params);
   B200_LAUNCH_OK();
+  return 0;
+}
+
+// Image pass only, against a colour table that is already complete (built by
+// b200_lab3_classify's LUT variant or cooperatively by b200_lab3_lut_build_allgather).
+extern "C" int b200_lab3_apply_lut(void* img, int64_t npix, const void* lut, b200_stream_t s) {
+  if (npix <= 0) return 0;
+  cudaStream_t st = as_stream(s);
+  const int sms = device_info().sm_count;
+  const bool aligned = (((uintptr_t)img) & 15u) == 0;
+  const int64_t n_vec = aligned ? npix / 4 : 0;
+  const int64_t tail = n_vec * 4;
+  auto grid_for = [&](int64_t items) {
+    int64_t want = (items + kClsThreads - 1) / kClsThreads;
+    int64_t cap = (int64_t)sms * 8;
+    return (int)(want < cap ? (want > 0 ? want : 1) : cap);
+  };
+  if (n_vec) {
+    lab3_lut_apply_kernel<<<grid_for(n_vec), kClsThreads, 0, st>>>((uint32_t*)img, n_vec,
+                                                                   (const uint8_t*)lut);
+    B200_LAUNCH_OK();
+  }
+  if (tail < npix) {
+    lab3_lut_apply_scalar_kernel<<<grid_for(npix - tail), kClsThreads, 0, st>>>(
+        (uint32_t*)img, tail, npix, (const uint8_t*)lut);
+    B200_LAUNCH_OK();
+  }
   return 0;
 }

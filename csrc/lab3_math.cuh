@@ -2,7 +2,13 @@
 #pragma once
 #include "common.cuh"
 
+#include <cfloat>
+
 namespace b200 {
+
+constexpr int kNP = B200_LAB3_PARAMS;
+constexpr int kNM = B200_LAB3_MOMENTS;
+constexpr int kMaxC = B200_LAB3_MAX_CLASSES;
 
 // moments -> mean + inverse covariance.  Same formulas as b200_cpu_lab3_finalize
 // (oracle.cpp); every product/sum uses an explicit-rounding intrinsic so nothing
@@ -34,6 +40,56 @@ __device__ __forceinline__ void lab3_finalize_class(const long long* m, double* 
       out[3 + a * 3 + b] =
           __ddiv_rn(sub(mul(cov[b1][a1], cov[b2][a2]), mul(cov[b1][a2], cov[b2][a1])), det);
     }
+}
+
+
+// distance of colour (r,g,b) to one class: the reference's operation chain
+//   temp[i] = fma(d2,m[2][i], fma(d1,m[1][i], fma(d0,m[0][i], 0)))
+//   dist    = fma(d2,temp[2], fma(d1,temp[1], fma(d0,temp[0], 0)))
+__device__ __forceinline__ double maha(double r, double g, double b, const double* p) {
+  const double d0 = __dsub_rn(r, p[0]), d1 = __dsub_rn(g, p[1]), d2 = __dsub_rn(b, p[2]);
+  double t0 = __fma_rn(d0, p[3], 0.0), t1 = __fma_rn(d0, p[4], 0.0), t2 = __fma_rn(d0, p[5], 0.0);
+  t0 = __fma_rn(d1, p[6], t0), t1 = __fma_rn(d1, p[7], t1), t2 = __fma_rn(d1, p[8], t2);
+  t0 = __fma_rn(d2, p[9], t0), t1 = __fma_rn(d2, p[10], t1), t2 = __fma_rn(d2, p[11], t2);
+  double dist = __fma_rn(d0, t0, 0.0);
+  dist = __fma_rn(d1, t1, dist);
+  return __fma_rn(d2, t2, dist);
+}
+
+template <int NPX>
+__device__ __forceinline__ void classify_group(const uint32_t (&px)[NPX], int nc,
+                                               const double* sp, int (&best)[NPX]) {
+  double r[NPX], g[NPX], b[NPX], mind[NPX];
+#pragma unroll
+  for (int k = 0; k < NPX; ++k) {
+    r[k] = (double)(px[k] & 0xff);
+    g[k] = (double)((px[k] >> 8) & 0xff);
+    b[k] = (double)((px[k] >> 16) & 0xff);
+    mind[k] = DBL_MAX;
+    best[k] = -1;
+  }
+  for (int c = 0; c < nc; ++c) {
+    double p[kNP];
+#pragma unroll
+    for (int j = 0; j < kNP; ++j) p[j] = sp[c * kNP + j];
+#pragma unroll
+    for (int k = 0; k < NPX; ++k) {
+      const double d = maha(r[k], g[k], b[k], p);
+      if (d < mind[k]) {
+        mind[k] = d;
+        best[k] = c;
+      }
+    }
+  }
+}
+
+__device__ __forceinline__ uint32_t set_alpha(uint32_t px, int cls) {
+  return (px & 0x00ffffffu) | ((uint32_t)(cls & 0xff) << 24);
+}
+
+__device__ __forceinline__ void load_params_smem(double* sp, const double* params, int nc) {
+  for (int i = threadIdx.x; i < nc * kNP; i += blockDim.x) sp[i] = params[i];
+  __syncthreads();
 }
 
 

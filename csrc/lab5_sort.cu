@@ -6,7 +6,7 @@
 //   1. one histogram kernel reads the keys once and builds all four digit
 //      histograms (privatised per warp in shared memory);
 //   2. per pass ONE kernel ranks and scatters: tiles of 8192 keys take a ticket,
-//      rank their keys with warp match-any, publish the tile's digit counts and
+//      rank their keys with a warp-wide ballot match, publish the tile's digit counts and
 //      resolve their global offsets by decoupled look-back over earlier tiles
 //      (single 64-bit status|pass|value words, so no fences and one zero-fill
 //      serves all four passes), stage the keys in shared memory in digit order and
@@ -144,24 +144,26 @@ __global__ void __launch_bounds__(kSortThreads, 2)
     key[i] = o < n_valid ? ld_stream_u32(in + tile_base + o) : 0xffffffffu;
   }
 
-  // ---- rank inside the warp: match-any on the digit, leader bumps the counter
+  // ---- rank inside the warp: lanes with my digit (ballot match), the highest of
+  // them bumps the warp's counter for that digit and broadcasts the old value
   uint16_t rank[kItems];
   uint32_t* wh = S.warp_hist[warp];
-  const uint32_t lt_mask = (1u << lane) - 1;
+  const uint32_t le_mask = 0xffffffffu >> (31 - lane);
 #pragma unroll
   for (int i = 0; i < kItems; ++i) {
     const bool valid = (w_off + i * 32) < n_valid;
     // padding keys rank as digit 255 *after* every real key (they come last)
     const uint32_t d = valid ? ((to_ordered<KT>(key[i]) >> shift) & 0xff) : 0xffu;
-    const uint32_t peers = __match_any_sync(0xffffffffu, d);
-    const int leader = __ffs(peers) - 1;
+    const uint32_t peers = match_any_bits<kRadixBits>(d);
+    const int leader = 31 - __clz(peers);
+    const uint32_t below_incl = __popc(peers & le_mask);  // on the leader: the group size
     uint32_t old = 0;
     if (lane == leader) {
       old = wh[d];
-      wh[d] = old + __popc(peers);
+      wh[d] = old + below_incl;
     }
     old = __shfl_sync(0xffffffffu, old, leader);
-    rank[i] = (uint16_t)(old + __popc(peers & lt_mask));
+    rank[i] = (uint16_t)(old + below_incl - 1);
     __syncwarp();
   }
   __syncthreads();

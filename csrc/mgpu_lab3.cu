@@ -115,9 +115,74 @@ __global__ void __launch_bounds__(kStatThreads)
   }
 }
 
+// ---- colour table built cooperatively: 1/world of the 2^24 colours per rank ----
+// Each rank classifies its slice of the colour cube with the usual DFMA chain and
+// stores the packed class bytes into EVERY rank's table (remote 128-byte-per-warp
+// stores), so the table build scales with the GPU count instead of being repeated
+// on every GPU; the last CTA fences, signals all peers and waits for them, after
+// which the local table is complete and the image pass can gather from it.
+constexpr int kLutThreads = 256;
+
+struct LutTargets {
+  uint32_t* lut4[kMaxWorld];  // every rank's table, peer-mapped, as packed uint32
+};
+
+__global__ void __launch_bounds__(kLutThreads)
+    lab3_lut_build_allgather_kernel(LutTargets tg, int nc, const double* __restrict__ params,
+                                    SymmPeers peers, int rank, int world, uint64_t epoch,
+                                    int phase_mask, unsigned long long timeout_ns) {
+  __shared__ double sp[kMaxC * kNP];
+  __shared__ bool is_last;
+  SymmWorkspace* me = peers.ws[rank];
+  const int tid = threadIdx.x;
+  if (phase_mask & 1) {
+    load_params_smem(sp, params, nc);
+    const uint32_t per_rank = (1u << 22) / world;  // packed words per rank
+    const uint32_t t = rank * per_rank + blockIdx.x * kLutThreads + tid;
+    uint32_t px[4] = {4 * t, 4 * t + 1, 4 * t + 2, 4 * t + 3};
+    int best[4];
+    classify_group<4>(px, nc, sp, best);
+    const uint32_t word = (uint32_t)(best[0] & 0xff) | ((uint32_t)(best[1] & 0xff) << 8) |
+                          ((uint32_t)(best[2] & 0xff) << 16) | ((uint32_t)(best[3] & 0xff) << 24);
+    for (int p = 0; p < world; ++p) tg.lut4[(rank + p) % world][t] = word;  // own copy first
+    __threadfence_system();
+    __syncthreads();
+    if (tid == 0) is_last = atomicAdd(&me->lab3_lut_blocks_done, 1u) == gridDim.x - 1;
+    __syncthreads();
+    if (!is_last) return;
+    if (tid == 0) me->lab3_lut_blocks_done = 0;
+    __threadfence_system();
+    if (tid < world) signal_peer(peers, tid, rank, epoch, kFlagLab3Lut);
+  }
+  if (phase_mask & 2) {
+    if (tid < world) wait_peer(peers, rank, tid, epoch, timeout_ns, kFlagLab3Lut);
+  }
+}
+
 }  // namespace b200
 
 using namespace b200;
+
+// Cooperative colour-table build (see kernel comment).  lut_ptrs: HOST array [world]
+// of the peer-mapped 16 MiB tables.  After the call (stream order) the local table
+// is complete; follow with b200_lab3_apply_lut.  phase_mask as for the statistics.
+extern "C" int b200_lab3_lut_build_allgather(void* const* lut_ptrs, int nc, const double* params,
+                                             const void* ws_ptrs, int rank, int world,
+                                             uint64_t epoch, int phase_mask, b200_stream_t s) {
+  B200_REQUIRE(nc > 0 && nc <= kLab3C, "lab3: class count %d outside 1..%d", nc, kLab3C);
+  B200_REQUIRE(world >= 1 && world <= kMaxWorld && (world & (world - 1)) == 0 && rank >= 0 &&
+                   rank < world,
+               "lab3: lut all-gather needs a power-of-two world <= %d (rank %d, world %d)",
+               kMaxWorld, rank, world);
+  LutTargets tg;
+  for (int p = 0; p < kMaxWorld; ++p) tg.lut4[p] = p < world ? (uint32_t*)lut_ptrs[p] : nullptr;
+  SymmPeers peers{(SymmWorkspace* const*)ws_ptrs};
+  const unsigned grid = (phase_mask & 1) ? ((1u << 22) / world) / kLutThreads : 1u;
+  lab3_lut_build_allgather_kernel<<<grid, kLutThreads, 0, as_stream(s)>>>(
+      tg, nc, params, peers, rank, world, epoch, phase_mask, kDefaultTimeoutNs);
+  B200_LAUNCH_OK();
+  return 0;
+}
 
 // Fused statistics + all-reduce + finalize.  ws_ptrs: device array [world] of the
 // peer-mapped SymmWorkspace of every rank; epoch must grow by one per call (the

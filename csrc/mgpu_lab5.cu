@@ -145,7 +145,7 @@ __global__ void __launch_bounds__(kPartThreads, 2)
     uint8_t dst[kPartItems];
     uint16_t rk[kPartItems];
     const uint32_t w_off = warp * (kPartItems * 32) + lane;
-    const uint32_t lt_mask = (1u << lane) - 1;
+    const uint32_t le_mask = 0xffffffffu >> (31 - lane);
 #pragma unroll
     for (int i = 0; i < kPartItems; ++i) {
       const uint32_t o = w_off + i * 32;
@@ -161,15 +161,16 @@ __global__ void __launch_bounds__(kPartThreads, 2)
         d = kMaxWorld;  // padding: no destination
       }
       dst[i] = (uint8_t)d;
-      const uint32_t peers_mask = __match_any_sync(0xffffffffu, d);
-      const int leader = __ffs(peers_mask) - 1;
+      const uint32_t peers_mask = match_any_bits<4>((uint32_t)d);  // d <= kMaxWorld = 8
+      const int leader = 31 - __clz(peers_mask);
+      const uint32_t below_incl = __popc(peers_mask & le_mask);
       uint32_t old = 0;
       if (valid && lane == leader) {
         old = warp_cnt[warp][d];
-        warp_cnt[warp][d] = old + __popc(peers_mask);
+        warp_cnt[warp][d] = old + below_incl;
       }
       old = __shfl_sync(0xffffffffu, old, leader);
-      rk[i] = (uint16_t)(old + __popc(peers_mask & lt_mask));
+      rk[i] = (uint16_t)(old + below_incl - 1);
       __syncwarp();
     }
     __syncthreads();

@@ -11,7 +11,9 @@ constexpr unsigned long long kDefaultTimeoutNs = 20ull * 1000 * 1000 * 1000;  //
 constexpr int kLab3C = B200_LAB3_MAX_CLASSES, kLab3M = B200_LAB3_MOMENTS;
 constexpr int kSortMaxSamplesTotal = 8192;  // world * samples_per_rank, sorted in one CTA
 
-enum SymmFlag { kFlagBarrier = 0, kFlagLab3 = 1, kFlagSortSamples = 2, kFlagSortDone = 3, kNumFlags = 4 };
+enum SymmFlag {
+  kFlagBarrier = 0, kFlagLab3 = 1, kFlagSortSamples = 2, kFlagSortDone = 3, kFlagLab3Lut = 4, kNumFlags = 5
+};
 enum SymmError { kErrTimeout = 1, kErrSortOverflow = 2 };
 
 // One of these lives on every rank at a symmetric (peer-mapped) address.  Fields
@@ -22,7 +24,7 @@ struct SymmWorkspace {
   // ---- lab3: in-kernel all-reduce of the class moments
   long long lab3_acc[kLab3C][kLab3M];                 // this rank's partial sums
   unsigned int lab3_blocks_done;
-  unsigned int pad0;
+  unsigned int lab3_lut_blocks_done;
   long long lab3_slots[2][kMaxWorld][kLab3C][kLab3M];  // [remote] slots[epoch&1][sender]
   // ---- lab5: sample exchange + bucket cursor for the fused all-to-all
   unsigned long long sort_cursor;        // [remote atomics] next free index of my bucket

@@ -29,6 +29,10 @@ from .symm import PeerGroup, SymmetricBuffer
 N.register("b200_lab3_stats_allreduce", C.c_int,
            [C.c_void_p, C.c_int, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p,
             C.c_int, C.c_int, C.c_uint64, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p])
+N.register("b200_lab3_lut_build_allgather", C.c_int,
+           [C.POINTER(C.c_void_p), C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_uint64, C.c_int,
+            C.c_void_p])
+N.register("b200_lab3_apply_lut", C.c_int, [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p])
 N.register("b200_sort_mgpu_splitters", C.c_int,
            [C.c_void_p, C.c_size_t, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_uint64, C.c_int,
             C.c_void_p])
@@ -114,8 +118,26 @@ def fused_stats(img: torch.Tensor, w: int, y0: int, h_local: int, d_pts: torch.T
         "b200_lab3_stats_allreduce")
 
 
+def lut_build_allgather(lut_ptrs: Sequence[int], nc: int, params: torch.Tensor, ws_ptrs_dev: torch.Tensor,
+                        rank: int, world: int, epoch: int, phase_mask: int = 3) -> None:
+    N.check(N.lib().b200_lab3_lut_build_allgather(_ptr_array(lut_ptrs), nc, N.ptr(params), N.ptr(ws_ptrs_dev),
+                                                  rank, world, epoch, phase_mask, N.current_stream_ptr()),
+            "b200_lab3_lut_build_allgather")
+
+
+def apply_lut(img: torch.Tensor, lut_addr: int) -> torch.Tensor:
+    N.check(N.lib().b200_lab3_apply_lut(N.ptr(img), img.shape[0] * img.shape[1], C.c_void_p(lut_addr),
+                                        N.current_stream_ptr()), "b200_lab3_apply_lut")
+    return img
+
+
 class ShardedClassifier:
-    """Row-sharded lab3: global sample points, statistics all-reduced, local classify."""
+    """Row-sharded lab3: global sample points, statistics all-reduced, local classify.
+    With the fused implementation on several GPUs the 2^24-entry colour table is built
+    cooperatively (each rank classifies 1/world of the colours and stores them into
+    every rank's table over NVLink).  The table is rewritten every step; the in-kernel
+    all-reduce of the next step's statistics is what orders a peer's rewrite after this
+    rank's image pass, so always call ``step()`` (fit + classify), not classify alone."""
 
     def __init__(self, group: PeerGroup, w: int, h_total: int, classes, impl: str = "fused",
                  variant: str = "auto"):
@@ -136,6 +158,8 @@ class ShardedClassifier:
         self.scratch = torch.empty(need, dtype=torch.uint8, device=dev) if need else None
         self.ws = group.workspace()
         lut = need > 0
+        self.coop_lut = lut and impl == "fused" and group.world > 1 and group.world & (group.world - 1) == 0
+        self.sym_lut = group.alloc(1 << 24) if self.coop_lut else None
         # kernels per step: stats(1) [+ finalize for nccl] + classify (lut: build + apply)
         self.launches_per_step = (1 if impl == "fused" else 2) + (2 if lut else 1)
 
@@ -153,7 +177,17 @@ class ShardedClassifier:
 
     def step(self) -> torch.Tensor:
         self.fit()
+        if self.coop_lut:
+            g = self.group
+            lut_build_allgather(self.sym_lut.peer_ptrs, self.nc, self.params, self.ws.ptrs_dev, g.rank,
+                                g.world, g.next_epoch(), 3)
+            return apply_lut(self.band, self.sym_lut.local_ptr)
         return CL.lab3_classify(self.band, self.params, variant=self.variant, scratch=self.scratch)
+
+    def free(self) -> None:
+        if self.sym_lut is not None:
+            self.sym_lut.free()
+            self.sym_lut = None
 
 
 # ------------------------------------------------------------------------- lab5

@@ -166,6 +166,15 @@ int b200_lab3_stats_allreduce(const void* img, int w, int64_t y0, int64_t h_loca
                               double* params, long long* moments_out, int phase_mask,
                               b200_stream_t s);
 
+/* lab3 colour table built cooperatively: each rank classifies 1/world of the 2^24
+ * colours and stores the class bytes into every rank's 16 MiB table (lut_ptrs: HOST
+ * array [world] of peer-mapped tables); then the image pass against the finished
+ * table.  Same decisions as b200_lab3_classify, the build just scales with N. */
+int b200_lab3_lut_build_allgather(void* const* lut_ptrs, int nc, const double* params,
+                                  const void* ws_ptrs, int rank, int world, uint64_t epoch,
+                                  int phase_mask, b200_stream_t s);
+int b200_lab3_apply_lut(void* img, int64_t npix, const void* lut, b200_stream_t s);
+
 /* lab5 fused sample sort, step 1: sample + exchange + splitters (one CTA). */
 int b200_sort_mgpu_splitters(const void* keys, size_t n_local, int key_type,
                              int samples_per_rank, const void* ws_ptrs, int rank, int world,

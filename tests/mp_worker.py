@@ -33,16 +33,19 @@ def main():
     classes = [np.stack([rng.integers(0, w, 500), rng.integers(0, h, 500)], axis=1) for _ in range(nc)]
     p_want = MahalanobisClassifier.reference_params(img, classes, mode="moments")
     c_want = MahalanobisClassifier.reference_classify(img, p_want)
-    for impl in ("fused", "nccl"):
-        m = ShardedClassifier(g, w, h, classes, impl=impl)
+    for impl, variant in (("fused", "auto"), ("nccl", "auto"), ("fused", "lut"), ("nccl", "lut")):
+        m = ShardedClassifier(g, w, h, classes, impl=impl, variant=variant)
+        assert m.coop_lut == (impl == "fused" and variant == "lut")
         for rep in range(3):
             m.band.copy_(torch.from_numpy(img[m.y0:m.y1].copy()).view(torch.int32).reshape(m.h_local, w))
             g.barrier()
             out = m.step()
             assert np.array_equal(m.params.cpu().numpy().view(np.int64), p_want.view(np.int64)), f"lab3 params {impl}"
             got = out.cpu().numpy().view(np.uint8).reshape(m.h_local, w, 4)
-            assert np.array_equal(got, c_want[m.y0:m.y1]), f"lab3 classify {impl} rank {rank}"
+            assert np.array_equal(got, c_want[m.y0:m.y1]), f"lab3 classify {impl}/{variant} rank {rank}"
         assert g.ws_error() == 0
+        g.barrier()
+        m.free()
 
     n_local = 300_000 + 11
     for impl in ("fused", "nccl"):

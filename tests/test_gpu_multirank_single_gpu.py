@@ -61,6 +61,34 @@ def test_lab3_stats_allreduce_matches_single_gpu_bitwise(cuda_device, world):
     assert all(int(w_.local[group.ranks[0].ws_offset("error"):][:8].view(torch.int64).item()) == 0 for w_ in ws)
 
 
+@pytest.mark.parametrize("world", [1, 2, 8])
+def test_lab3_cooperative_lut_matches_oracle(cuda_device, world):
+    rng = np.random.default_rng(60 + world)
+    h, w, nc = 96, 128, 32
+    img = rng.integers(0, 256, size=(h, w, 4), dtype=np.uint8)
+    classes = [np.stack([rng.integers(0, w, 200), rng.integers(0, h, 200)], axis=1) for _ in range(nc)]
+    params = MahalanobisClassifier.reference_params(img, classes, mode="moments")
+    want = MahalanobisClassifier.reference_classify(img, params)
+    d_params = torch.from_numpy(params).to(cuda_device)
+    group = LocalPeerGroup(world, cuda_device)
+    ws = group.workspaces()
+    luts = group.alloc(1 << 24)
+    epoch = group.next_epoch()
+    for r in range(world):        # every rank classifies its slice of the colour cube into ALL tables
+        S.lut_build_allgather(luts[r].peer_ptrs, nc, d_params, ws[r].ptrs_dev, r, world, epoch, 1)
+    for r in range(world):
+        S.lut_build_allgather(luts[r].peer_ptrs, nc, d_params, ws[r].ptrs_dev, r, world, epoch, 2)
+    bands = shard_rows(h, world)
+    for r, (a, b) in enumerate(bands):
+        d = torch.from_numpy(img[a:b].copy()).to(cuda_device)
+        S.apply_lut(d, luts[r].local_ptr)
+        assert np.array_equal(d.cpu().numpy(), want[a:b]), r
+    torch.cuda.synchronize()
+    assert torch.equal(luts[0].local, luts[world - 1].local)
+    for b in luts:
+        b.free()
+
+
 @pytest.mark.parametrize("world", [2, 4, 8])
 @pytest.mark.parametrize("dtype,kind", [(np.int32, "random"), (np.float32, "random"), (np.int32, "dups"),
                                         (np.int32, "equal"), (np.uint32, "skewed")])
