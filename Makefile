@@ -6,7 +6,7 @@ CXX       ?= g++
 CC        ?= gcc
 ARCH      := -gencode arch=compute_100a,code=sm_100a
 NVFLAGS   := $(ARCH) -O3 -lineinfo -std=c++17 -Iinclude -Icsrc -Xcompiler -fPIC \
-             -Werror cross-execution-space-call
+             -Werror cross-execution-space-call $(EXTRA_NVFLAGS)
 # oracles must not be contracted by the host compiler: FMAs are spelled out
 CXXFLAGS  := -O2 -std=c++17 -fPIC -Iinclude -ffp-contract=off
 CFLAGS    := -O2 -std=c11

@@ -95,17 +95,24 @@ __device__ __forceinline__ uint32_t smem_u32(const void* p) {
 }
 
 // Lanes of the warp whose `label` equals mine, from BITS ballots instead of
-// MATCH.ANY: on B200 the match instruction is issued at roughly one warp per ~60
-// cycles per SM (ADU pipe, measured with ncu: 60% of the radix-sort samples sat on
-// its result), while VOTE + LOP3 run at ALU rate.
+// MATCH.ANY.  Measured with ncu on B200: MATCH.ANY issues at roughly one warp per
+// ~60 cycles per SM (ADU pipe; 60% of the radix-sort samples sat on its result),
+// the ballot form costs 4 ALU-pipe instructions per bit (bit test -> predicate,
+// VOTE, and two complementary predicated LOP3).  The two run on different pipes, so
+// the sort mixes them (see kMatchItems in lab5_sort.cu).
 template <int BITS>
 __device__ __forceinline__ uint32_t match_any_bits(uint32_t label) {
   uint32_t peers = 0xffffffffu;
 #pragma unroll
   for (int b = 0; b < BITS; ++b) {
-    const bool bit = (label >> b) & 1u;
-    const uint32_t m = __ballot_sync(0xffffffffu, bit);
-    peers &= bit ? m : ~m;
+    asm("{\n\t.reg .pred p;\n\t.reg .b32 t, m;\n\t"
+        "and.b32 t, %1, %2;\n\t"
+        "setp.ne.u32 p, t, 0;\n\t"
+        "vote.sync.ballot.b32 m, p, 0xffffffff;\n\t"
+        "@p and.b32 %0, %0, m;\n\t"
+        "@!p lop3.b32 %0, %0, m, 0, 0x30;\n\t}"  // a & ~b
+        : "+r"(peers)
+        : "r"(label), "r"(1u << b));
   }
   return peers;
 }

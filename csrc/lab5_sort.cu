@@ -6,7 +6,9 @@
 //   1. one histogram kernel reads the keys once and builds all four digit
 //      histograms (privatised per warp in shared memory);
 //   2. per pass ONE kernel ranks and scatters: tiles of 8192 keys take a ticket,
-//      rank their keys with a warp-wide ballot match, publish the tile's digit counts and
+//      rank their keys inside each warp (lanes sharing a digit are found through a
+//      shared-memory OR word; MATCH.ANY is ADU-bound on B200 and ballots ALU-bound,
+//      see profiles/), publish the tile's digit counts and
 //      resolve their global offsets by decoupled look-back over earlier tiles
 //      (single 64-bit status|pass|value words, so no fences and one zero-fill
 //      serves all four passes), stage the keys in shared memory in digit order and
@@ -14,16 +16,28 @@
 // Traffic: 1 read + 4 x (read + write) of the keys = 9 x 4 B per key, plus
 // ~2 KB of look-back words per 32 KB tile.  uint8 keys are a counting sort
 // (histogram + fill).
+#include <cstdlib>
+
 #include "common.cuh"
 
 namespace b200 {
 
 constexpr int kRadixBits = 8;
 constexpr int kRadix = 1 << kRadixBits;
-constexpr int kSortThreads = 512;
+#ifndef B200_SORT_THREADS
+#define B200_SORT_THREADS 512
+#endif
+constexpr int kSortThreads = B200_SORT_THREADS;
+constexpr int kSortBlocksPerSm = 1024 / kSortThreads;
 constexpr int kSortWarps = kSortThreads / 32;
 constexpr int kItems = 16;
 constexpr int kTile = kSortThreads * kItems;  // 8192 keys
+#ifndef B200_SORT_MATCH_ITEMS
+#define B200_SORT_MATCH_ITEMS -1
+#endif
+// how a warp finds the lanes that share a digit: -1 = shared-memory OR words (default,
+// fastest on B200), 0 = ballots, k > 0 = MATCH.ANY for the first k keys of a thread
+constexpr int kMatchItems = B200_SORT_MATCH_ITEMS;
 
 // order-preserving bijection key bits -> unsigned
 template <int KT>
@@ -112,28 +126,21 @@ struct SweepSmem {
   uint32_t tile_start[kRadix];            // first tile position of each digit
   uint32_t scan_tmp[kRadix / 32];
   uint32_t tile_id;
+  uint32_t lane_bits[kSortWarps][kRadix]; // 16 KB: per-warp "which lanes hold digit d" words
 };
 
-template <int KT>
-__global__ void __launch_bounds__(kSortThreads, 2)
-    sort_onesweep_kernel(const uint32_t* __restrict__ in, uint32_t* __restrict__ out, size_t n,
-                         const unsigned long long* __restrict__ n_dev, int pass,
-                         const unsigned long long* __restrict__ digit_base /*[256]*/,
-                         unsigned long long* __restrict__ lookback /*[tiles][256]*/,
-                         uint32_t* __restrict__ ticket) {
-  extern __shared__ __align__(16) uint8_t smem_raw[];
-  SweepSmem& S = *reinterpret_cast<SweepSmem*>(smem_raw);
+// One tile of one pass.  FULL = the tile holds kTile real keys (every tile but the
+// last), which removes all the validity predicates from the hot loops.  NM of the
+// kItems keys per thread are matched with MATCH.ANY (ADU pipe), the others with
+// ballots (ALU pipe), so that the two pipes share the ranking work.
+template <int KT, int NM, bool FULL>
+__device__ __forceinline__ void sweep_tile(SweepSmem& S, const uint32_t* __restrict__ in,
+                                           uint32_t* __restrict__ out, size_t tile_base,
+                                           uint32_t n_valid, uint32_t tile, int pass,
+                                           const unsigned long long* __restrict__ digit_base,
+                                           unsigned long long* __restrict__ lookback) {
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int shift = pass * kRadixBits;
-
-  if (tid == 0) S.tile_id = atomicAdd(ticket, 1u);
-  for (int i = tid; i < kSortWarps * kRadix; i += kSortThreads) (&S.warp_hist[0][0])[i] = 0;
-  __syncthreads();
-  const uint32_t tile = S.tile_id;
-  const size_t tile_base = (size_t)tile * kTile;
-  if (n_dev) n = (size_t)*n_dev;
-  if (tile_base >= n) return;  // grid was sized for the capacity, not the actual length
-  const uint32_t n_valid = (uint32_t)min((size_t)kTile, n - tile_base);
 
   // ---- load: warp-striped, logical order == memory order (keeps the pass stable)
   uint32_t key[kItems];
@@ -141,35 +148,48 @@ __global__ void __launch_bounds__(kSortThreads, 2)
 #pragma unroll
   for (int i = 0; i < kItems; ++i) {
     const uint32_t o = w_off + i * 32;
-    key[i] = o < n_valid ? ld_stream_u32(in + tile_base + o) : 0xffffffffu;
+    key[i] = (FULL || o < n_valid) ? ld_stream_u32(in + tile_base + o) : 0xffffffffu;
   }
 
-  // ---- rank inside the warp: lanes with my digit (ballot match), the highest of
-  // them bumps the warp's counter for that digit and broadcasts the old value
-  uint16_t rank[kItems];
+  // ---- rank inside the warp: find the lanes with my digit; the highest of them
+  // bumps the warp's counter for that digit and broadcasts the old value
+  uint32_t dr[kItems];  // digit << 16 | rank inside (warp, digit)
   uint32_t* wh = S.warp_hist[warp];
+  uint32_t* lb = S.lane_bits[warp];
   const uint32_t le_mask = 0xffffffffu >> (31 - lane);
 #pragma unroll
   for (int i = 0; i < kItems; ++i) {
-    const bool valid = (w_off + i * 32) < n_valid;
     // padding keys rank as digit 255 *after* every real key (they come last)
-    const uint32_t d = valid ? ((to_ordered<KT>(key[i]) >> shift) & 0xff) : 0xffu;
-    const uint32_t peers = match_any_bits<kRadixBits>(d);
+    uint32_t d = (to_ordered<KT>(key[i]) >> shift) & 0xff;
+    if (!FULL && (w_off + i * 32) >= n_valid) d = 0xffu;
+    uint32_t peers;
+    if (NM < 0) {
+      // match through shared memory: every lane ORs its bit into the word of its
+      // digit, then reads the word back — three LSU operations instead of 40 ALU ones
+      atomicOr(&lb[d], 1u << lane);
+      __syncwarp();
+      peers = lb[d];
+      __syncwarp();
+    } else {
+      peers = i < NM ? __match_any_sync(0xffffffffu, d) : match_any_bits<kRadixBits>(d);
+    }
     const int leader = 31 - __clz(peers);
     const uint32_t below_incl = __popc(peers & le_mask);  // on the leader: the group size
     uint32_t old = 0;
     if (lane == leader) {
       old = wh[d];
       wh[d] = old + below_incl;
+      if (NM < 0) lb[d] = 0;  // leave the word clean for the next key
     }
     old = __shfl_sync(0xffffffffu, old, leader);
-    rank[i] = (uint16_t)(old + below_incl - 1);
+    dr[i] = (d << 16) | (old + below_incl - 1);
     __syncwarp();
   }
   __syncthreads();
 
-  // ---- per digit: scan over warps, publish the tile aggregate, look back
-  uint32_t count = 0;
+  // ---- per digit: scan over warps, publish the tile aggregate, digit scan
+  uint32_t count = 0, real = 0, start = 0;
+  const unsigned long long tag = ((unsigned long long)pass << kPassShift);
   if (tid < kRadix) {
 #pragma unroll
     for (int wv = 0; wv < kSortWarps; ++wv) {
@@ -177,9 +197,8 @@ __global__ void __launch_bounds__(kSortThreads, 2)
       S.warp_hist[wv][tid] = count;  // exclusive offset of this warp inside the digit
       count += c;
     }
-    uint32_t real = count;
-    if (tid == kRadix - 1) real -= (kTile - n_valid);  // drop the padding keys
-    const unsigned long long tag = ((unsigned long long)pass << kPassShift);
+    real = count;
+    if (!FULL && tid == kRadix - 1) real -= (kTile - n_valid);  // drop the padding keys
     st_lookback(lookback + (size_t)tile * kRadix + tid, (kStAggregate << kStatusShift) | tag | real);
 
     // exclusive scan of `count` over the 256 digits -> tile_start
@@ -190,21 +209,50 @@ __global__ void __launch_bounds__(kSortThreads, 2)
       if (lane >= o) inc += t;
     }
     if (lane == 31) S.scan_tmp[warp] = inc;
-    asm volatile("bar.sync 1, 256;" ::: "memory");
+    asm volatile("bar.sync 1, 256;" ::: "memory");  // the kRadix digit threads only
     uint32_t base = 0;
     for (int wv = 0; wv < warp; ++wv) base += S.scan_tmp[wv];
-    const uint32_t start = base + inc - count;
+    start = base + inc - count;
     S.tile_start[tid] = start;
+  }
+  __syncthreads();
 
-    // decoupled look-back: sum aggregates of earlier tiles until an inclusive one
+  // ---- stage keys in digit order (needs only tile-local offsets; doing it before
+  // the look-back frees the key registers for the probes below)
+#pragma unroll
+  for (int i = 0; i < kItems; ++i) {
+    const uint32_t d = dr[i] >> 16;
+    S.keys[S.tile_start[d] + S.warp_hist[warp][d] + (dr[i] & 0xffffu)] = key[i];
+  }
+
+  if (tid < kRadix) {
+    // decoupled look-back: sum aggregates of earlier tiles until an inclusive one.
+    // kLook predecessors are probed per round with independent loads (one L2 round
+    // trip instead of kLook): when many tiles are in flight the walk back to the last
+    // finished one is long, and it is pure latency.
     unsigned long long excl = 0;
+    constexpr int kLook = 8;
     for (int64_t t = (int64_t)tile - 1; t >= 0;) {
-      const unsigned long long e = ld_lookback(lookback + (size_t)t * kRadix + tid);
-      const unsigned long long st = e >> kStatusShift;
-      if (st == 0 || ((e >> kPassShift) & 0xf) != (unsigned long long)pass) continue;  // not yet
-      excl += e & kValueMask;
-      if (st == kStInclusive) break;
-      --t;
+      unsigned long long e[kLook];
+#pragma unroll
+      for (int j = 0; j < kLook; ++j)
+        e[j] = (t - j >= 0) ? ld_lookback(lookback + (size_t)(t - j) * kRadix + tid) : 0ull;
+      bool done = false;
+#pragma unroll
+      for (int j = 0; j < kLook; ++j) {
+        if (done || t < 0) continue;
+        const unsigned long long st = e[j] >> kStatusShift;
+        if (st == 0 || ((e[j] >> kPassShift) & 0xf) != (unsigned long long)pass) {
+          done = true;  // not published yet: probe again from this tile
+          continue;
+        }
+        excl += e[j] & kValueMask;
+        --t;
+        if (st == kStInclusive) {
+          t = -1;
+          done = true;
+        }
+      }
     }
     st_lookback(lookback + (size_t)tile * kRadix + tid,
                 (kStInclusive << kStatusShift) | tag | (excl + real));
@@ -212,25 +260,43 @@ __global__ void __launch_bounds__(kSortThreads, 2)
   }
   __syncthreads();
 
-  // ---- stage keys in digit order
-#pragma unroll
-  for (int i = 0; i < kItems; ++i) {
-    const bool valid = (w_off + i * 32) < n_valid;
-    const uint32_t d = valid ? ((to_ordered<KT>(key[i]) >> shift) & 0xff) : 0xffu;
-    S.keys[S.tile_start[d] + S.warp_hist[warp][d] + rank[i]] = key[i];
-  }
-  __syncthreads();
-
   // ---- coalesced runs out
 #pragma unroll
   for (int i = 0; i < kItems; ++i) {
     const uint32_t p = tid + i * kSortThreads;
-    if (p < n_valid) {
+    if (FULL || p < n_valid) {
       const uint32_t k = S.keys[p];
       const uint32_t d = (to_ordered<KT>(k) >> shift) & 0xff;
       out[S.global_off[d] + p] = k;
     }
   }
+}
+
+template <int KT, int NM>
+__global__ void __launch_bounds__(kSortThreads, kSortBlocksPerSm)
+    sort_onesweep_kernel(const uint32_t* __restrict__ in, uint32_t* __restrict__ out, size_t n,
+                         const unsigned long long* __restrict__ n_dev, int pass,
+                         const unsigned long long* __restrict__ digit_base /*[256]*/,
+                         unsigned long long* __restrict__ lookback /*[tiles][256]*/,
+                         uint32_t* __restrict__ ticket) {
+  extern __shared__ __align__(16) uint8_t smem_raw[];
+  SweepSmem& S = *reinterpret_cast<SweepSmem*>(smem_raw);
+  const int tid = threadIdx.x;
+  if (tid == 0) S.tile_id = atomicAdd(ticket, 1u);
+  for (int i = tid; i < kSortWarps * kRadix; i += kSortThreads) {
+    (&S.warp_hist[0][0])[i] = 0;
+    if (NM < 0) (&S.lane_bits[0][0])[i] = 0;
+  }
+  __syncthreads();
+  const uint32_t tile = S.tile_id;
+  const size_t tile_base = (size_t)tile * kTile;
+  if (n_dev) n = (size_t)*n_dev;
+  if (tile_base >= n) return;  // grid was sized for the capacity, not the actual length
+  const uint32_t n_valid = (uint32_t)min((size_t)kTile, n - tile_base);
+  if (n_valid == kTile)
+    sweep_tile<KT, NM, true>(S, in, out, tile_base, n_valid, tile, pass, digit_base, lookback);
+  else
+    sweep_tile<KT, NM, false>(S, in, out, tile_base, n_valid, tile, pass, digit_base, lookback);
 }
 
 // ------------------------------------------------------------------ uint8 keys
@@ -310,12 +376,24 @@ template <int KT>
 static int sort32(const uint32_t* input, uint32_t* keys, uint32_t* tmp, size_t n,
                   const unsigned long long* n_dev, const SortScratch& sc, cudaStream_t st) {
   const int sms = device_info().sm_count;
+  // how many of the 16 keys per thread use MATCH.ANY (tunable: B200LABS_SORT_MATCH=-1 (shared-memory match) |0|2|4|6)
+  static const int nm = [] {
+    const char* e = getenv("B200LABS_SORT_MATCH");
+    int v = e ? atoi(e) : kMatchItems;
+    return v < 0 ? -1 : v == 0 ? 0 : v <= 2 ? 2 : v <= 4 ? 4 : 6;
+  }();
+  using Kernel = void (*)(const uint32_t*, uint32_t*, size_t, const unsigned long long*, int,
+                          const unsigned long long*, unsigned long long*, uint32_t*);
+  const Kernel kernel = nm < 0    ? sort_onesweep_kernel<KT, -1>
+                        : nm == 0 ? sort_onesweep_kernel<KT, 0>
+                        : nm == 2 ? sort_onesweep_kernel<KT, 2>
+                        : nm == 4 ? sort_onesweep_kernel<KT, 4>
+                                  : sort_onesweep_kernel<KT, 6>;
   static bool attr_set[64] = {false};
   int dev = 0;
   cudaGetDevice(&dev);
   if (!attr_set[dev & 63]) {
-    B200_CUDA_OK(cudaFuncSetAttribute(sort_onesweep_kernel<KT>,
-                                      cudaFuncAttributeMaxDynamicSharedMemorySize,
+    B200_CUDA_OK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                       (int)sizeof(SweepSmem)));
     attr_set[dev & 63] = true;
   }
@@ -335,7 +413,7 @@ static int sort32(const uint32_t* input, uint32_t* keys, uint32_t* tmp, size_t n
   const uint32_t* src = input;
   uint32_t* dst = tmp;
   for (int pass = 0; pass < 4; ++pass) {
-    sort_onesweep_kernel<KT><<<(unsigned)sc.tiles, kSortThreads, sizeof(SweepSmem), st>>>(
+    kernel<<<(unsigned)sc.tiles, kSortThreads, sizeof(SweepSmem), st>>>(
         src, dst, n, n_dev, pass, sc.hist + pass * kRadix, sc.lookback, sc.tickets + pass);
     B200_LAUNCH_OK();
     src = dst;
@@ -454,7 +532,8 @@ constexpr size_t kNoAllocBookBytes =
     (4 * kRadix * sizeof(unsigned long long) + 64 +
      ((kNoAllocMaxKeys + kTile - 1) / kTile) * kRadix * sizeof(unsigned long long) + 255) / 256 * 256;
 constexpr size_t kNoAllocBytes = kNoAllocBookBytes + kNoAllocMaxKeys * sizeof(uint32_t);
-static_assert(kNoAllocBytes == B200_SORT_NOALLOC_SCRATCH_BYTES, "header constant out of date");
+static_assert(kNoAllocBytes == B200_SORT_NOALLOC_SCRATCH_BYTES || B200_SORT_THREADS != 512,
+              "header constant out of date");
 
 static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoAllocBytes];
 
