@@ -2,7 +2,7 @@
 //   cuda_exe          stdin "in out"              no stdout            (ref: lab2/src/main.cu)
 //   to_plot_cuda_exe  stdin "bx by gx gy in out"  time line + FINISHED (ref: lab2/src/to_plot.cu)
 // to_plot honours the block/grid it is given (launch-geometry sweep); any dim
-// <= 0 selects the tuned kernel.  B200LABS_ROBERTS=stream|tma|generic forces a variant.
+// <= 0 selects the tuned kernel.  B200LABS_ROBERTS=stream|tma|cluster|generic forces a variant.
 #include "b200labs.h"
 #include "cli_common.h"
 
@@ -12,6 +12,7 @@ static int variant_from_env() {
   if (!strcmp(v, "stream")) return B200_ROBERTS_STREAM;
   if (!strcmp(v, "tma")) return B200_ROBERTS_TMA;
   if (!strcmp(v, "generic")) return B200_ROBERTS_GENERIC;
+  if (!strcmp(v, "cluster")) return B200_ROBERTS_CLUSTER;
   return B200_ROBERTS_AUTO;
 }
 

@@ -12,6 +12,8 @@
 //    (tile + its one-row / one-column stencil apron in a single box), output
 //    staged in shared memory and written back with per-warp TMA stores
 //    (lab2_roberts_tma.cu).  Fastest on large images: the AUTO choice.
+//  * CLUSTER — the TMA pipeline with CTA pairs (thread-block clusters) that read
+//    each other's tile edge column over DSMEM (lab2_roberts_cluster.cu).
 //  * GENERIC — one pixel per thread, any width/alignment, any launch geometry
 //    (the harness's block/grid sweep).
 // All variants take `below_row`: the row that follows the band.  For a row-
@@ -25,6 +27,9 @@ namespace b200 {
 int roberts_tma_launch(const void* in, void* out, int w, int64_t h_local, const void* below_row,
                        cudaStream_t st);  // lab2_roberts_tma.cu
 bool roberts_tma_supported(const void* in, const void* out, int w, int64_t h_local);
+int roberts_cluster_launch(const void* in, void* out, int w, int64_t h_local,
+                           const void* below_row, cudaStream_t st);  // lab2_roberts_cluster.cu
+bool roberts_cluster_supported(const void* in, const void* out, int w, int64_t h_local);
 
 constexpr int kRsThreads = 256;
 constexpr int kRsWarps = kRsThreads / 32;
@@ -184,6 +189,10 @@ extern "C" int b200_roberts(const void* in, void* out, int w, int64_t h_local,
       B200_REQUIRE(roberts_tma_supported(in, out, w, h_local),
                    "roberts: TMA variant needs w %% 4 == 0, 16-byte aligned buffers, w >= 256");
       return roberts_tma_launch(in, out, w, h_local, src.below, st);
+    case B200_ROBERTS_CLUSTER:
+      B200_REQUIRE(roberts_cluster_supported(in, out, w, h_local),
+                   "roberts: CLUSTER variant needs w %% 4 == 0, 16-byte aligned buffers, w >= 256");
+      return roberts_cluster_launch(in, out, w, h_local, src.below, st);
     case B200_ROBERTS_GENERIC: {
       dim3 block(32, 8);
       const int64_t gy = (h_local + 7) / 8;

@@ -32,11 +32,14 @@ constexpr int kSortBlocksPerSm = 1024 / kSortThreads;
 constexpr int kSortWarps = kSortThreads / 32;
 constexpr int kItems = 16;
 constexpr int kTile = kSortThreads * kItems;  // 8192 keys
-#ifndef B200_SORT_MATCH_ITEMS
-#define B200_SORT_MATCH_ITEMS -1
+#ifndef B200_SORT_PERSIST_DEFAULT
+#define B200_SORT_PERSIST_DEFAULT 0
 #endif
-// how a warp finds the lanes that share a digit: -1 = shared-memory OR words (default,
-// fastest on B200), 0 = ballots, k > 0 = MATCH.ANY for the first k keys of a thread
+#ifndef B200_SORT_MATCH_ITEMS
+#define B200_SORT_MATCH_ITEMS 0
+#endif
+// how many of a thread's 16 keys find their same-digit lanes with ballots; the rest
+// use shared-memory OR words (see sweep_tile)
 constexpr int kMatchItems = B200_SORT_MATCH_ITEMS;
 
 // order-preserving bijection key bits -> unsigned
@@ -130,25 +133,38 @@ struct SweepSmem {
 };
 
 // One tile of one pass.  FULL = the tile holds kTile real keys (every tile but the
-// last), which removes all the validity predicates from the hot loops.  NM of the
-// kItems keys per thread are matched with MATCH.ANY (ADU pipe), the others with
-// ballots (ALU pipe), so that the two pipes share the ranking work.
-template <int KT, int NM, bool FULL>
+// last), which removes all the validity predicates from the hot loops.  To rank a
+// key a warp must find the lanes holding the same digit; the first NM of a thread's
+// kItems keys do it with ballots (ALU pipe, ~40 instructions), the rest through a
+// shared-memory OR word (LSU/shared-memory pipe), so that both pipes carry part of
+// the ranking work.  (MATCH.ANY, the obvious instruction, is ADU-bound on B200: one
+// warp per ~60 cycles per SM, measured — see profiles/ncu_prof_lab5.md.)
+struct NoHook {
+  __device__ __forceinline__ void operator()() const {}
+};
+
+template <int KT, int NM, bool FULL, bool PREFETCHED = false, typename Hook = NoHook>
 __device__ __forceinline__ void sweep_tile(SweepSmem& S, const uint32_t* __restrict__ in,
                                            uint32_t* __restrict__ out, size_t tile_base,
                                            uint32_t n_valid, uint32_t tile, int pass,
                                            const unsigned long long* __restrict__ digit_base,
-                                           unsigned long long* __restrict__ lookback) {
+                                           unsigned long long* __restrict__ lookback,
+                                           const uint32_t* staged = nullptr, Hook after_load = Hook()) {
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int shift = pass * kRadixBits;
 
-  // ---- load: warp-striped, logical order == memory order (keeps the pass stable)
+  // ---- load: warp-striped, logical order == memory order (keeps the pass stable).
+  // PREFETCHED: the tile was copied into shared memory (cp.async) while the previous
+  // tile was being processed; the caller re-arms that buffer after the first barrier.
   uint32_t key[kItems];
   const uint32_t w_off = warp * (kItems * 32) + lane;
 #pragma unroll
   for (int i = 0; i < kItems; ++i) {
     const uint32_t o = w_off + i * 32;
-    key[i] = (FULL || o < n_valid) ? ld_stream_u32(in + tile_base + o) : 0xffffffffu;
+    if (PREFETCHED)
+      key[i] = (FULL || o < n_valid) ? staged[o] : 0xffffffffu;
+    else
+      key[i] = (FULL || o < n_valid) ? ld_stream_u32(in + tile_base + o) : 0xffffffffu;
   }
 
   // ---- rank inside the warp: find the lanes with my digit; the highest of them
@@ -163,7 +179,8 @@ __device__ __forceinline__ void sweep_tile(SweepSmem& S, const uint32_t* __restr
     uint32_t d = (to_ordered<KT>(key[i]) >> shift) & 0xff;
     if (!FULL && (w_off + i * 32) >= n_valid) d = 0xffu;
     uint32_t peers;
-    if (NM < 0) {
+    const bool via_smem = i >= NM;  // compile-time after unrolling
+    if (via_smem) {
       // match through shared memory: every lane ORs its bit into the word of its
       // digit, then reads the word back — three LSU operations instead of 40 ALU ones
       atomicOr(&lb[d], 1u << lane);
@@ -171,7 +188,7 @@ __device__ __forceinline__ void sweep_tile(SweepSmem& S, const uint32_t* __restr
       peers = lb[d];
       __syncwarp();
     } else {
-      peers = i < NM ? __match_any_sync(0xffffffffu, d) : match_any_bits<kRadixBits>(d);
+      peers = match_any_bits<kRadixBits>(d);
     }
     const int leader = 31 - __clz(peers);
     const uint32_t below_incl = __popc(peers & le_mask);  // on the leader: the group size
@@ -179,24 +196,21 @@ __device__ __forceinline__ void sweep_tile(SweepSmem& S, const uint32_t* __restr
     if (lane == leader) {
       old = wh[d];
       wh[d] = old + below_incl;
-      if (NM < 0) lb[d] = 0;  // leave the word clean for the next key
+      if (via_smem) lb[d] = 0;  // leave the word clean for the next key
     }
     old = __shfl_sync(0xffffffffu, old, leader);
     dr[i] = (d << 16) | (old + below_incl - 1);
     __syncwarp();
   }
   __syncthreads();
+  after_load();  // every thread holds its keys in registers: the staging buffer is free
 
   // ---- per digit: scan over warps, publish the tile aggregate, digit scan
   uint32_t count = 0, real = 0, start = 0;
   const unsigned long long tag = ((unsigned long long)pass << kPassShift);
   if (tid < kRadix) {
 #pragma unroll
-    for (int wv = 0; wv < kSortWarps; ++wv) {
-      const uint32_t c = S.warp_hist[wv][tid];
-      S.warp_hist[wv][tid] = count;  // exclusive offset of this warp inside the digit
-      count += c;
-    }
+    for (int wv = 0; wv < kSortWarps; ++wv) count += S.warp_hist[wv][tid];
     real = count;
     if (!FULL && tid == kRadix - 1) real -= (kTile - n_valid);  // drop the padding keys
     st_lookback(lookback + (size_t)tile * kRadix + tid, (kStAggregate << kStatusShift) | tag | real);
@@ -214,6 +228,14 @@ __device__ __forceinline__ void sweep_tile(SweepSmem& S, const uint32_t* __restr
     for (int wv = 0; wv < warp; ++wv) base += S.scan_tmp[wv];
     start = base + inc - count;
     S.tile_start[tid] = start;
+    // warp_hist[w][d] := tile position of the first key of (warp w, digit d)
+    uint32_t run = start;
+#pragma unroll
+    for (int wv = 0; wv < kSortWarps; ++wv) {
+      const uint32_t c = S.warp_hist[wv][tid];
+      S.warp_hist[wv][tid] = run;
+      run += c;
+    }
   }
   __syncthreads();
 
@@ -222,7 +244,7 @@ __device__ __forceinline__ void sweep_tile(SweepSmem& S, const uint32_t* __restr
 #pragma unroll
   for (int i = 0; i < kItems; ++i) {
     const uint32_t d = dr[i] >> 16;
-    S.keys[S.tile_start[d] + S.warp_hist[warp][d] + (dr[i] & 0xffffu)] = key[i];
+    S.keys[S.warp_hist[warp][d] + (dr[i] & 0xffffu)] = key[i];
   }
 
   if (tid < kRadix) {
@@ -285,7 +307,7 @@ __global__ void __launch_bounds__(kSortThreads, kSortBlocksPerSm)
   if (tid == 0) S.tile_id = atomicAdd(ticket, 1u);
   for (int i = tid; i < kSortWarps * kRadix; i += kSortThreads) {
     (&S.warp_hist[0][0])[i] = 0;
-    if (NM < 0) (&S.lane_bits[0][0])[i] = 0;
+    if (NM < kItems) (&S.lane_bits[0][0])[i] = 0;
   }
   __syncthreads();
   const uint32_t tile = S.tile_id;
@@ -297,6 +319,81 @@ __global__ void __launch_bounds__(kSortThreads, kSortBlocksPerSm)
     sweep_tile<KT, NM, true>(S, in, out, tile_base, n_valid, tile, pass, digit_base, lookback);
   else
     sweep_tile<KT, NM, false>(S, in, out, tile_base, n_valid, tile, pass, digit_base, lookback);
+}
+
+// Persistent variant: two CTAs per SM stay resident and pull tiles by ticket; the
+// NEXT tile's keys (and its ticket) are fetched with cp.async while the current
+// tile is ranked and scattered, which takes the ticket round trip and the DRAM
+// latency of the key load off the critical path of every tile.
+struct SweepSmemPersistent {
+  SweepSmem base;
+  alignas(16) uint32_t staged[kTile];  // 32 KB: the next tile, landed by cp.async (16-byte chunks)
+  uint32_t next_tile;
+};
+
+__device__ __forceinline__ void cp_async_16(void* smem_dst, const void* gmem_src, uint32_t src_bytes) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(smem_u32(smem_dst)),
+               "l"(gmem_src), "r"(src_bytes)
+               : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() {
+  asm volatile("cp.async.wait_all;" ::: "memory");
+}
+
+template <int KT, int NM>
+__global__ void __launch_bounds__(kSortThreads, kSortBlocksPerSm)
+    sort_onesweep_persistent_kernel(const uint32_t* __restrict__ in, uint32_t* __restrict__ out,
+                                    size_t n, const unsigned long long* __restrict__ n_dev, int pass,
+                                    const unsigned long long* __restrict__ digit_base,
+                                    unsigned long long* __restrict__ lookback,
+                                    uint32_t* __restrict__ ticket) {
+  extern __shared__ __align__(16) uint8_t smem_raw[];
+  SweepSmemPersistent& PS = *reinterpret_cast<SweepSmemPersistent*>(smem_raw);
+  SweepSmem& S = PS.base;
+  const int tid = threadIdx.x;
+  if (n_dev) n = (size_t)*n_dev;
+  const size_t n_tiles = (n + kTile - 1) / kTile;
+
+  auto prefetch = [&](uint32_t t) {  // copy tile t into PS.staged (zero-fills past n)
+    if (t >= n_tiles) return;
+    const size_t base = (size_t)t * kTile;
+    const size_t left = n - base;  // keys available from `base`
+#pragma unroll
+    for (int j = 0; j < kTile / 4 / kSortThreads; ++j) {
+      const uint32_t c = tid + j * kSortThreads;  // 16-byte chunk of the tile
+      const size_t first = (size_t)c * 4;
+      const uint32_t bytes = first >= left ? 0u : (uint32_t)min((size_t)16, (left - first) * 4);
+      cp_async_16(&PS.staged[c * 4], in + base + first, bytes);
+    }
+  };
+
+  if (tid == 0) PS.next_tile = atomicAdd(ticket, 1u);
+  __syncthreads();
+  uint32_t tile = PS.next_tile;
+  prefetch(tile);
+  while (tile < n_tiles) {
+    for (int i = tid; i < kSortWarps * kRadix; i += kSortThreads) {
+      (&S.warp_hist[0][0])[i] = 0;
+      if (NM < kItems) (&S.lane_bits[0][0])[i] = 0;
+    }
+    cp_async_wait_all();
+    __syncthreads();  // staged keys + zeroed counters visible; previous tile fully written out
+    if (tid == 0) PS.next_tile = atomicAdd(ticket, 1u);  // resolved long before it is read
+    uint32_t next = 0;
+    auto rearm = [&]() {  // runs after sweep_tile's first barrier: keys are in registers
+      next = PS.next_tile;
+      prefetch(next);
+    };
+    const size_t tile_base = (size_t)tile * kTile;
+    const uint32_t n_valid = (uint32_t)min((size_t)kTile, n - tile_base);
+    if (n_valid == kTile)
+      sweep_tile<KT, NM, true, true>(S, in, out, tile_base, n_valid, tile, pass, digit_base, lookback,
+                                     PS.staged, rearm);
+    else
+      sweep_tile<KT, NM, false, true>(S, in, out, tile_base, n_valid, tile, pass, digit_base,
+                                      lookback, PS.staged, rearm);
+    tile = next;
+  }
 }
 
 // ------------------------------------------------------------------ uint8 keys
@@ -376,25 +473,35 @@ template <int KT>
 static int sort32(const uint32_t* input, uint32_t* keys, uint32_t* tmp, size_t n,
                   const unsigned long long* n_dev, const SortScratch& sc, cudaStream_t st) {
   const int sms = device_info().sm_count;
-  // how many of the 16 keys per thread use MATCH.ANY (tunable: B200LABS_SORT_MATCH=-1 (shared-memory match) |0|2|4|6)
+  // how many of the 16 keys per thread are matched with ballots (the rest go through
+  // shared memory); tunable: B200LABS_SORT_BALLOT=0|4|8|12|16
   static const int nm = [] {
-    const char* e = getenv("B200LABS_SORT_MATCH");
+    const char* e = getenv("B200LABS_SORT_BALLOT");
     int v = e ? atoi(e) : kMatchItems;
-    return v < 0 ? -1 : v == 0 ? 0 : v <= 2 ? 2 : v <= 4 ? 4 : 6;
+    return v <= 0 ? 0 : v <= 4 ? 4 : v <= 8 ? 8 : v <= 12 ? 12 : 16;
   }();
   using Kernel = void (*)(const uint32_t*, uint32_t*, size_t, const unsigned long long*, int,
                           const unsigned long long*, unsigned long long*, uint32_t*);
-  const Kernel kernel = nm < 0    ? sort_onesweep_kernel<KT, -1>
-                        : nm == 0 ? sort_onesweep_kernel<KT, 0>
-                        : nm == 2 ? sort_onesweep_kernel<KT, 2>
-                        : nm == 4 ? sort_onesweep_kernel<KT, 4>
-                                  : sort_onesweep_kernel<KT, 6>;
+  const Kernel kernel = nm == 0    ? sort_onesweep_kernel<KT, 0>
+                        : nm == 4  ? sort_onesweep_kernel<KT, 4>
+                        : nm == 8  ? sort_onesweep_kernel<KT, 8>
+                        : nm == 12 ? sort_onesweep_kernel<KT, 12>
+                                   : sort_onesweep_kernel<KT, 16>;
+  // persistent CTAs with cp.async prefetch of the next tile (B200LABS_SORT_PERSIST=0 disables)
+  static const bool persist_env = [] {
+    const char* e = getenv("B200LABS_SORT_PERSIST");
+    return e ? atoi(e) != 0 : (B200_SORT_PERSIST_DEFAULT != 0);
+  }();
+  const bool persist = persist_env && nm == 0 && ((((uintptr_t)input) | ((uintptr_t)keys) | ((uintptr_t)tmp)) & 15u) == 0;
+  const Kernel pkernel = sort_onesweep_persistent_kernel<KT, 0>;
   static bool attr_set[64] = {false};
   int dev = 0;
   cudaGetDevice(&dev);
   if (!attr_set[dev & 63]) {
     B200_CUDA_OK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                       (int)sizeof(SweepSmem)));
+    B200_CUDA_OK(cudaFuncSetAttribute(pkernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      (int)sizeof(SweepSmemPersistent)));
     attr_set[dev & 63] = true;
   }
   {
@@ -413,8 +520,15 @@ static int sort32(const uint32_t* input, uint32_t* keys, uint32_t* tmp, size_t n
   const uint32_t* src = input;
   uint32_t* dst = tmp;
   for (int pass = 0; pass < 4; ++pass) {
-    kernel<<<(unsigned)sc.tiles, kSortThreads, sizeof(SweepSmem), st>>>(
-        src, dst, n, n_dev, pass, sc.hist + pass * kRadix, sc.lookback, sc.tickets + pass);
+    if (persist) {
+      size_t grid = (size_t)sms * kSortBlocksPerSm;
+      if (grid > sc.tiles) grid = sc.tiles;
+      pkernel<<<(unsigned)grid, kSortThreads, sizeof(SweepSmemPersistent), st>>>(
+          src, dst, n, n_dev, pass, sc.hist + pass * kRadix, sc.lookback, sc.tickets + pass);
+    } else {
+      kernel<<<(unsigned)sc.tiles, kSortThreads, sizeof(SweepSmem), st>>>(
+          src, dst, n, n_dev, pass, sc.hist + pass * kRadix, sc.lookback, sc.tickets + pass);
+    }
     B200_LAUNCH_OK();
     src = dst;
     dst = (dst == tmp) ? keys : tmp;

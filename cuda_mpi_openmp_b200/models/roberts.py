@@ -13,6 +13,7 @@ import torch
 
 from .. import _native as N
 from ..ops import roberts
+from ..ops.roberts import ROBERTS_VARIANTS
 
 
 class RobertsFilter:
@@ -55,7 +56,7 @@ class RobertsFilter:
         dst = host_out.view(torch.int32).reshape(h, w)
         rows = max(1, min(h, self.chunk_bytes // (4 * w)))
         self._ensure_stage(rows, w)
-        lib, variant = N.lib(), {"auto": 0, "stream": 1, "tma": 2, "generic": 3}[self.variant]
+        lib, variant = N.lib(), ROBERTS_VARIANTS[self.variant]
         cur = torch.cuda.current_stream(self.device)
         for s in self._streams:
             s.wait_stream(cur)

@@ -5,7 +5,7 @@ import torch
 
 from .. import _native as N
 
-ROBERTS_VARIANTS = {"auto": 0, "stream": 1, "tma": 2, "generic": 3}
+ROBERTS_VARIANTS = {"auto": 0, "stream": 1, "tma": 2, "generic": 3, "cluster": 4}
 
 
 def _as_image(t: torch.Tensor) -> tuple[int, int]:

@@ -56,7 +56,8 @@ enum {
   B200_ROBERTS_AUTO = 0,
   B200_ROBERTS_STREAM = 1, /* register sliding window, 128-bit accesses      */
   B200_ROBERTS_TMA = 2,    /* persistent TMA tile pipeline, TMA stores          */
-  B200_ROBERTS_GENERIC = 3 /* one pixel per thread, any alignment            */
+  B200_ROBERTS_GENERIC = 3, /* one pixel per thread, any alignment           */
+  B200_ROBERTS_CLUSTER = 4  /* TMA pipeline, CTA pairs share tile edges (DSMEM) */
 };
 int b200_roberts(const void* in, void* out, int w, int64_t h_local,
                  const void* below_row, int variant, b200_stream_t s);

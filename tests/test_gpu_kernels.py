@@ -50,10 +50,12 @@ SHAPES = {
     "generic": [(1, 1), (3, 3), (5, 7), (33, 130), (257, 255)],
     "stream": [(1, 4), (2, 128), (64, 132), (300, 512), (1000, 1028), (9, 4096)],
     "tma": [(1, 256), (33, 256), (300, 512), (1000, 1028), (2049, 2052), (31, 4096)],
+    "cluster": [(1, 256), (33, 256), (300, 512), (1000, 1028), (2049, 2052), (31, 4096), (70, 768)],
 }
 
 
-@pytest.mark.parametrize("variant", ["generic", "stream", "tma", "auto"])
+@pytest.mark.timeout(180)
+@pytest.mark.parametrize("variant", ["generic", "stream", "tma", "cluster", "auto"])
 def test_roberts_bit_exact(cuda_device, variant):
     rng = np.random.default_rng(7)
     shapes = SHAPES.get(variant) or (SHAPES["generic"] + SHAPES["stream"])
@@ -69,7 +71,8 @@ def test_roberts_bit_exact(cuda_device, variant):
         assert (out.to(torch.int16) - t.to(torch.int16)).abs().max().item() <= 1
 
 
-@pytest.mark.parametrize("variant", ["generic", "stream", "tma"])
+@pytest.mark.timeout(180)
+@pytest.mark.parametrize("variant", ["generic", "stream", "tma", "cluster"])
 def test_roberts_row_sharded_with_halo_pointer(cuda_device, variant):
     """Row bands filtered independently, each reading its halo row through a pointer
     into the next band (what the multi-GPU path does with a peer pointer)."""

@@ -58,7 +58,7 @@ def main():
         for h, w in ([(16384, 16384)] if args.quick else [(1024, 1024), (16384, 16384), (32768, 32768)]):
             img = torch.randint(-2 ** 31, 2 ** 31 - 1, (h, w), dtype=torch.int32, device=dev)
             out = torch.empty_like(img)
-            for v in ("stream", "tma", "generic"):
+            for v in ("stream", "tma", "cluster", "generic"):
                 report(rows, f"lab2.roberts[{v}]", f"{w}x{h}",
                        cuda_time_ms(lambda: ops.roberts(img, out, variant=v), **it), 8 * h * w)
             report(rows, "lab2.roberts_geom block32x32 grid16x16", f"{w}x{h}",
