@@ -33,6 +33,12 @@ struct SymmWorkspace {
   unsigned long long sort_samples[kSortMaxSamplesTotal];  // [remote] composites, by sender
   unsigned long long sort_splitters[kMaxWorld];
   unsigned long long sort_recv_count;    // keys that landed in my bucket (device-side n)
+  // exact two-phase reservation: how many of MY keys go to each rank, and where my
+  // segment inside that rank's bucket begins / how far I have filled it
+  unsigned long long sort_send_count[kMaxWorld];
+  unsigned long long sort_local_cursor[kMaxWorld];
+  unsigned int sort_count_blocks_done;
+  unsigned int pad2;
 };
 
 struct SymmPeers {

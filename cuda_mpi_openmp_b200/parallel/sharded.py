@@ -40,6 +40,8 @@ N.register("b200_sort_mgpu_scatter", C.c_int,
            [C.c_void_p, C.c_size_t, C.c_int, C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p),
             C.c_size_t, C.c_void_p, C.POINTER(C.c_void_p), C.c_int, C.c_int, C.c_uint64, C.c_int,
             C.c_void_p])
+N.register("b200_sort_mgpu_count", C.c_int,
+           [C.c_void_p, C.c_size_t, C.c_int, C.c_void_p, C.c_size_t, C.c_void_p, C.c_int, C.c_int, C.c_void_p])
 N.register("b200_sort_devn", C.c_int,
            [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_int, C.c_void_p, C.c_size_t, C.c_void_p])
 N.register("b200_sort_ex", C.c_int,
@@ -208,6 +210,13 @@ def mgpu_scatter(keys: torch.Tensor, splitters_addr: int, bucket_ptrs: Sequence[
         N.current_stream_ptr()), "b200_sort_mgpu_scatter")
 
 
+def mgpu_count(keys: torch.Tensor, splitters_addr: int, capacity: int, ws: SymmetricBuffer, rank: int,
+               world: int) -> None:
+    N.check(N.lib().b200_sort_mgpu_count(N.ptr(keys), keys.numel(), ST.KEY_TYPES[keys.dtype],
+                                         C.c_void_p(splitters_addr), capacity, N.ptr(ws.ptrs_dev), rank, world,
+                                         N.current_stream_ptr()), "b200_sort_mgpu_count")
+
+
 def sort_devn(bucket: torch.Tensor, tmp: torch.Tensor, count_addr: int, scratch: torch.Tensor) -> None:
     N.check(N.lib().b200_sort_devn(N.ptr(bucket), N.ptr(tmp), bucket.numel(), C.c_void_p(count_addr),
                                    ST.KEY_TYPES[bucket.dtype], N.ptr(scratch), scratch.numel(),
@@ -244,7 +253,7 @@ class ShardedSort:
             self.cursors = torch.zeros(world, dtype=torch.int64, device=dev)
             self.count_dev = torch.zeros(1, dtype=torch.int64, device=dev)
         # kernels per step: splitters + scatter + memset-free sort (hist, scan, 4 passes)
-        self.launches_per_step = (6 if world == 1 else 8)
+        self.launches_per_step = (6 if world == 1 else 9)
         self._count_host: Optional[int] = None
 
     def step(self) -> None:
@@ -260,8 +269,9 @@ class ShardedSort:
         ws_local = self.ws.local_ptr
         mgpu_splitters(self.keys, self.samples, self.ws.ptrs_dev, r, world, g.next_epoch(), 3)
         if self.impl == "fused":
+            mgpu_count(self.keys, ws_local + self._off["sort_splitters"], self.capacity, self.ws, r, world)
             mgpu_scatter(self.keys, ws_local + self._off["sort_splitters"], self.sym_bucket.peer_ptrs, None,
-                         self.capacity, self.ws, r, world, g.next_epoch(), 3)
+                         self.capacity, self.ws, r, world, g.next_epoch(), 1 | 2 | 8)
             sort_devn(self.bucket, self.tmp, ws_local + self._off["sort_recv_count"], self.scratch)
             return
         # ---- NCCL baseline: partition into local send segments, exchange with all_to_all

@@ -180,10 +180,17 @@ int b200_lab3_apply_lut(void* img, int64_t npix, const void* lut, b200_stream_t 
 int b200_sort_mgpu_splitters(const void* keys, size_t n_local, int key_type,
                              int samples_per_rank, const void* ws_ptrs, int rank, int world,
                              uint64_t epoch, int phase_mask, b200_stream_t s);
+/* step 1b: count this rank's keys per destination and reserve one contiguous segment
+ * in every destination bucket (one remote atomic each).  Follow with the scatter
+ * launched with phase bit 8 set, which then needs no remote atomics at all. */
+int b200_sort_mgpu_count(const void* keys, size_t n_local, int key_type, const void* splitters,
+                         size_t capacity, const void* ws_ptrs, int rank, int world,
+                         b200_stream_t s);
 /* step 2: partition fused with the all-to-all — keys are stored straight into the
  * destination ranks' buckets (bucket_ptrs: HOST array [world] of peer-mapped device
  * addresses), space reserved with one remote atomic per tile and destination.
- * phase_mask: 1 scatter+signal, 2 wait+publish count, 4 (with 1) local only. */
+ * phase_mask: 1 scatter+signal, 2 wait+publish count, 4 (with 1) local only,
+ * 8 segments were reserved by b200_sort_mgpu_count (tiles use local atomics). */
 int b200_sort_mgpu_scatter(const void* keys, size_t n_local, int key_type,
                            const void* splitters, void* const* bucket_ptrs,
                            void* const* cursor_ptrs, size_t capacity, const void* ws_ptrs,

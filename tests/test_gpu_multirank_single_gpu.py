@@ -125,12 +125,16 @@ def test_sample_sort_fused_scatter(cuda_device, world, dtype, kind):
     split0 = ws[0].local[off["sort_splitters"]:][: 8 * world].view(torch.int64).cpu()
     for r in range(1, world):               # every rank derived the same splitters
         assert torch.equal(ws[r].local[off["sort_splitters"]:][: 8 * world].view(torch.int64).cpu(), split0)
+    reserve = (world % 4 == 0)      # exercise both reservation schemes
+    if reserve:                     # exact two-phase: count, one remote atomic per destination
+        for r in range(world):
+            S.mgpu_count(d_keys[r], ws[r].local_ptr + off["sort_splitters"], capacity, ws[r], r, world)
     for r in range(world):
         S.mgpu_scatter(d_keys[r], ws[r].local_ptr + off["sort_splitters"], buckets[r].peer_ptrs, None, capacity,
-                       ws[r], r, world, e2, 1)
+                       ws[r], r, world, e2, 1 | (8 if reserve else 0))
     for r in range(world):
         S.mgpu_scatter(d_keys[r], ws[r].local_ptr + off["sort_splitters"], buckets[r].peer_ptrs, None, capacity,
-                       ws[r], r, world, e2, 2)
+                       ws[r], r, world, e2, 2 | (8 if reserve else 0))
     parts, counts = [], []
     for r in range(world):
         bucket = buckets[r].view(tdt, capacity)
