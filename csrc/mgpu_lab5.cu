@@ -41,6 +41,28 @@ __device__ __forceinline__ uint32_t hash32(uint32_t x) {
   return x;
 }
 
+// Destination rank of a key: the number of splitters <= its composite.  The 32-bit
+// ordered keys decide almost always; the (source, index) tie-break is consulted only
+// when some lane of the warp holds a key equal to a splitter's key.
+__device__ __forceinline__ int dest_of(uint32_t ordered, uint32_t low, const uint32_t* s_hi,
+                                       const uint32_t* s_lo, int world) {
+  int d = 0;
+  bool tie = false;
+#pragma unroll
+  for (int k = 1; k < kMaxWorld; ++k) {
+    if (k < world) {
+      d += s_hi[k] < ordered ? 1 : 0;
+      tie |= s_hi[k] == ordered;
+    }
+  }
+  if (__any_sync(0xffffffffu, tie)) {
+#pragma unroll
+    for (int k = 1; k < kMaxWorld; ++k)
+      if (k < world) d += (s_hi[k] == ordered && s_lo[k] <= low) ? 1 : 0;
+  }
+  return d;
+}
+
 constexpr int kSplitThreads = 1024;
 
 template <int KT>
@@ -113,9 +135,10 @@ __global__ void __launch_bounds__(kSplitThreads)
 // ------------------------------------------------------- count + segment reservation
 // One cheap read of the keys tells this rank how many of them go to each destination;
 // the last CTA then reserves ONE contiguous segment per destination with a single
-// remote atomic on that rank's bucket cursor.  (Reserving per tile instead — one
-// remote atomic per tile and destination — was measured at 15 ms for 2^30 keys on two
-// GPUs: a quarter of a million same-address atomics over NVLink serialise.)
+// remote atomic on that rank's bucket cursor.  Optional (B200LABS_SORT_RESERVE=1):
+// measured on 2 GPUs, 2^30 keys each, the count pass costs 2.0 ms and saves 0.6 ms
+// of per-tile remote atomics in the scatter, so the default path skips it; it is
+// kept because it makes the bucket layout (segments in rank order) deterministic.
 constexpr int kCountThreads = 256;
 constexpr int kCountItems = 16;
 
@@ -124,25 +147,66 @@ __global__ void __launch_bounds__(kCountThreads)
     sort_count_reserve_kernel(const uint32_t* __restrict__ keys, unsigned long long n_local,
                               const unsigned long long* __restrict__ splitters, int idx_bits,
                               unsigned long long capacity, SymmPeers peers, int rank, int world) {
-  __shared__ unsigned long long s_split[kMaxWorld];
+  __shared__ uint32_t s_hi[kMaxWorld], s_lo[kMaxWorld];
   __shared__ uint32_t s_cnt[kCountThreads / 32][kMaxWorld];
   __shared__ bool is_last;
   SymmWorkspace* me = peers.ws[rank];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  if (tid < kMaxWorld) s_split[tid] = tid < world ? splitters[tid] : ~0ull;
+  if (tid < kMaxWorld) {
+    const unsigned long long sp = tid < world ? splitters[tid] : ~0ull;
+    s_hi[tid] = (uint32_t)(sp >> 32);
+    s_lo[tid] = (uint32_t)sp;
+  }
   __syncthreads();
   uint32_t c[kMaxWorld];
 #pragma unroll
   for (int d = 0; d < kMaxWorld; ++d) c[d] = 0;
+  const uint32_t src_bits = idx_bits >= 32 ? 0u : ((uint32_t)rank << idx_bits);
+  // per-thread tally in eight 8-bit fields of one 64-bit word (one shift + add per key
+  // instead of eight compares), spilled into c[] before any field can reach 256
+  unsigned long long packed = 0;
+  int in_packed = 0;
+  auto flush = [&]() {
+#pragma unroll
+    for (int k = 0; k < kMaxWorld; ++k) c[k] += (uint32_t)(packed >> (8 * k)) & 0xffu;
+    packed = 0;
+    in_packed = 0;
+  };
+  // 16-byte loads, two per thread in flight; trip counts are warp-uniform so the
+  // vote inside dest_of always sees the whole warp
+  const unsigned long long n_vec = (((uintptr_t)keys) & 15u) == 0 ? n_local / 4 : 0;
   const unsigned long long stride = (unsigned long long)gridDim.x * kCountThreads;
-  for (unsigned long long i = (unsigned long long)blockIdx.x * kCountThreads + tid; i < n_local;
-       i += stride) {
-    const unsigned long long comp = make_composite(to_ordered_mg<KT>(ld_stream_u32(keys + i)), rank, i, idx_bits);
-    int d = 0;
+  const unsigned long long rounds = (n_vec + stride - 1) / stride;
+  for (unsigned long long r = 0; r < rounds; r += 2) {
+    const unsigned long long i0 = r * stride + (unsigned long long)blockIdx.x * kCountThreads + tid;
+    const unsigned long long i1 = i0 + stride;
+    uint4 v0 = make_uint4(0, 0, 0, 0), v1 = v0;
+    const bool ok0 = i0 < n_vec, ok1 = (r + 1 < rounds) && i1 < n_vec;
+    if (ok0) v0 = ld_stream_u4(keys + 4 * i0);
+    if (ok1) v1 = ld_stream_u4(keys + 4 * i1);
+    const uint32_t k0[4] = {v0.x, v0.y, v0.z, v0.w}, k1[4] = {v1.x, v1.y, v1.z, v1.w};
 #pragma unroll
-    for (int k = 1; k < kMaxWorld; ++k) d += (k < world && s_split[k] <= comp) ? 1 : 0;
+    for (int j = 0; j < 4; ++j) {
+      const int d0 = dest_of(to_ordered_mg<KT>(k0[j]), src_bits | (uint32_t)(4 * i0 + j), s_hi, s_lo, world);
+      const int d1 = dest_of(to_ordered_mg<KT>(k1[j]), src_bits | (uint32_t)(4 * i1 + j), s_hi, s_lo, world);
+      packed += (ok0 ? 1ull : 0ull) << (8 * d0);
+      packed += (ok1 ? 1ull : 0ull) << (8 * d1);
+    }
+    in_packed += 8;
+    if (in_packed > 240) flush();
+  }
+  flush();
+  {
+    const unsigned long long tail0 = n_vec * 4, left = n_local - tail0;
+    const unsigned long long tr = (left + stride - 1) / stride;
+    for (unsigned long long r = 0; r < tr; ++r) {
+      const unsigned long long i = tail0 + r * stride + (unsigned long long)blockIdx.x * kCountThreads + tid;
+      const bool ok = i < n_local;
+      const uint32_t key = ok ? keys[i] : 0u;
+      const int d = dest_of(to_ordered_mg<KT>(key), src_bits | (uint32_t)i, s_hi, s_lo, world);
 #pragma unroll
-    for (int k = 0; k < kMaxWorld; ++k) c[k] += (d == k) ? 1u : 0u;
+      for (int k = 0; k < kMaxWorld; ++k) c[k] += (ok && d == k) ? 1u : 0u;
+    }
   }
 #pragma unroll
   for (int d = 0; d < kMaxWorld; ++d) {
@@ -199,97 +263,111 @@ __global__ void __launch_bounds__(kPartThreads, 2)
   __shared__ uint32_t warp_cnt[kPartWarps][kMaxWorld];
   __shared__ uint32_t tile_start[kMaxWorld + 1];
   __shared__ unsigned long long base[kMaxWorld];
-  __shared__ unsigned long long s_split[kMaxWorld];
+  __shared__ uint32_t s_hi[kMaxWorld], s_lo[kMaxWorld];
+  __shared__ uint32_t* s_bucket[kMaxWorld];          // dynamically indexed: keep out of
+  __shared__ unsigned long long* s_cursor[kMaxWorld];  // param space (no local-memory copy)
   __shared__ bool is_last;
   SymmWorkspace* me = peers.ws[rank];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
   if (phase_mask & 1) {
-    if (tid < kMaxWorld) s_split[tid] = tid < world ? splitters[tid] : ~0ull;
-    for (int i = tid; i < kPartWarps * kMaxWorld; i += kPartThreads) (&warp_cnt[0][0])[i] = 0;
-    __syncthreads();
-    const unsigned long long tile_base = (unsigned long long)blockIdx.x * kPartTile;
-    const uint32_t n_valid = (uint32_t)min((unsigned long long)kPartTile, n_local - tile_base);
+    if (tid < kMaxWorld) {
+      const unsigned long long sp = tid < world ? splitters[tid] : ~0ull;
+      s_hi[tid] = (uint32_t)(sp >> 32);
+      s_lo[tid] = (uint32_t)sp;
+    }
+#pragma unroll
+    for (int k = 0; k < kMaxWorld; ++k)
+      if (tid == k) {
+        s_bucket[k] = tg.bucket[k];
+        s_cursor[k] = tg.cursor[k];
+      }
+    const uint32_t src_bits = idx_bits >= 32 ? 0u : ((uint32_t)rank << idx_bits);
+    const unsigned long long n_tiles = (n_local + kPartTile - 1) / kPartTile;
+    // persistent: a CTA walks tiles blockIdx.x, +gridDim.x, ... and fences its remote
+    // stores ONCE at the end (a system-scope fence per tile cost ~10 us of NVLink
+    // round trip per tile and made this kernel 3x slower)
+    for (unsigned long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+      for (int i = tid; i < kPartWarps * kMaxWorld; i += kPartThreads) (&warp_cnt[0][0])[i] = 0;
+      __syncthreads();  // also: previous tile's s_keys / tile_start / base fully consumed
+      const unsigned long long tile_base = tile * kPartTile;
+      const uint32_t n_valid = (uint32_t)min((unsigned long long)kPartTile, n_local - tile_base);
 
-    uint32_t key[kPartItems];
-    uint8_t dst[kPartItems];
-    uint16_t rk[kPartItems];
-    const uint32_t w_off = warp * (kPartItems * 32) + lane;
-    const uint32_t le_mask = 0xffffffffu >> (31 - lane);
+      uint32_t key[kPartItems];
+      uint32_t dr[kPartItems];  // destination << 16 | rank inside (warp, destination)
+      const uint32_t w_off = warp * (kPartItems * 32) + lane;
+      const uint32_t le_mask = 0xffffffffu >> (31 - lane);
 #pragma unroll
-    for (int i = 0; i < kPartItems; ++i) {
-      const uint32_t o = w_off + i * 32;
-      const bool valid = o < n_valid;
-      key[i] = valid ? ld_stream_u32(keys + tile_base + o) : 0u;
-      int d = 0;
-      if (valid) {
-        const unsigned long long comp =
-            make_composite(to_ordered_mg<KT>(key[i]), rank, tile_base + o, idx_bits);
+      for (int i = 0; i < kPartItems; ++i) {
+        const uint32_t o = w_off + i * 32;
+        key[i] = o < n_valid ? ld_stream_u32(keys + tile_base + o) : 0u;
+      }
 #pragma unroll
-        for (int k = 1; k < kMaxWorld; ++k) d += (k < world && s_split[k] <= comp) ? 1 : 0;
-      } else {
-        d = kMaxWorld;  // padding: no destination
-      }
-      dst[i] = (uint8_t)d;
-      const uint32_t peers_mask = match_any_bits<4>((uint32_t)d);  // d <= kMaxWorld = 8
-      const int leader = 31 - __clz(peers_mask);
-      const uint32_t below_incl = __popc(peers_mask & le_mask);
-      uint32_t old = 0;
-      if (valid && lane == leader) {
-        old = warp_cnt[warp][d];
-        warp_cnt[warp][d] = old + below_incl;
-      }
-      old = __shfl_sync(0xffffffffu, old, leader);
-      rk[i] = (uint16_t)(old + below_incl - 1);
-      __syncwarp();
-    }
-    __syncthreads();
-    // per destination: offsets of the warps, tile total, remote reservation
-    if (tid < world) {
-      uint32_t run = 0;
-      for (int wv = 0; wv < kPartWarps; ++wv) {
-        const uint32_t c = warp_cnt[wv][tid];
-        warp_cnt[wv][tid] = run;
-        run += c;
-      }
-      tile_start[tid + 1] = run;  // totals for now, scanned below
-      unsigned long long b = 0;
-      if (phase_mask & 8) {
-        // my segment in that rank's bucket was reserved by sort_count_reserve_kernel:
-        // sub-allocate it with a LOCAL atomic (no NVLink round trip on the tile's path)
-        if (run) b = atomicAdd(&me->sort_local_cursor[tid], (unsigned long long)run);
-        if (b + run > capacity) b = ~0ull;  // reservation failed earlier (error word is set)
-      } else {
-        if (run) b = atomicAdd_system(tg.cursor[tid], (unsigned long long)run);
-        if (b + run > capacity) {
-          atomicOr(&me->error, (unsigned long long)kErrSortOverflow);
-          b = ~0ull;  // poison: this tile's keys for that destination are dropped
+      for (int i = 0; i < kPartItems; ++i) {
+        const uint32_t o = w_off + i * 32;
+        const bool valid = o < n_valid;
+        int d = dest_of(to_ordered_mg<KT>(key[i]), src_bits | (uint32_t)(tile_base + o), s_hi, s_lo, world);
+        if (!valid) d = kMaxWorld;  // padding: no destination
+        const uint32_t peers_mask = match_any_bits<4>((uint32_t)d);  // d <= kMaxWorld = 8
+        const int leader = 31 - __clz(peers_mask);
+        const uint32_t below_incl = __popc(peers_mask & le_mask);
+        uint32_t old = 0;
+        if (valid && lane == leader) {
+          old = warp_cnt[warp][d];
+          warp_cnt[warp][d] = old + below_incl;
         }
+        old = __shfl_sync(0xffffffffu, old, leader);
+        dr[i] = ((uint32_t)d << 16) | (old + below_incl - 1);
+        __syncwarp();
       }
-      base[tid] = b;
-    }
-    __syncthreads();
-    if (tid == 0) {
-      tile_start[0] = 0;
-      for (int d = 0; d < world; ++d) tile_start[d + 1] += tile_start[d];
-    }
-    __syncthreads();
+      __syncthreads();
+      // per destination: offsets of the warps, tile total, reservation
+      if (tid < world) {
+        uint32_t run = 0;
+        for (int wv = 0; wv < kPartWarps; ++wv) {
+          const uint32_t c = warp_cnt[wv][tid];
+          warp_cnt[wv][tid] = run;
+          run += c;
+        }
+        tile_start[tid + 1] = run;  // totals for now, scanned below
+        unsigned long long b = 0;
+        if (phase_mask & 8) {
+          // my segment in that rank's bucket was reserved by sort_count_reserve_kernel:
+          // sub-allocate it with a LOCAL atomic (no NVLink round trip on the tile's path)
+          if (run) b = atomicAdd(&me->sort_local_cursor[tid], (unsigned long long)run);
+          if (b + run > capacity) b = ~0ull;  // reservation failed earlier (error word is set)
+        } else {
+          if (run) b = atomicAdd_system(s_cursor[tid], (unsigned long long)run);
+          if (b + run > capacity) {
+            atomicOr(&me->error, (unsigned long long)kErrSortOverflow);
+            b = ~0ull;  // poison: this tile's keys for that destination are dropped
+          }
+        }
+        base[tid] = b;
+      }
+      __syncthreads();
+      if (tid == 0) {
+        tile_start[0] = 0;
+        for (int d = 0; d < world; ++d) tile_start[d + 1] += tile_start[d];
+      }
+      __syncthreads();
 #pragma unroll
-    for (int i = 0; i < kPartItems; ++i) {
-      const int d = dst[i];
-      if (d < kMaxWorld) s_keys[tile_start[d] + warp_cnt[warp][d] + rk[i]] = key[i];
-    }
-    __syncthreads();
-    // runs of equal destination leave as contiguous remote stores
+      for (int i = 0; i < kPartItems; ++i) {
+        const int d = (int)(dr[i] >> 16);
+        if (d < kMaxWorld) s_keys[tile_start[d] + warp_cnt[warp][d] + (dr[i] & 0xffffu)] = key[i];
+      }
+      __syncthreads();
+      // runs of equal destination leave as contiguous (mostly remote) stores
 #pragma unroll
-    for (int i = 0; i < kPartItems; ++i) {
-      const uint32_t p = tid + i * kPartThreads;
-      if (p < n_valid) {
-        int d = 0;
+      for (int i = 0; i < kPartItems; ++i) {
+        const uint32_t p = tid + i * kPartThreads;
+        if (p < n_valid) {
+          int d = 0;
 #pragma unroll
-        for (int k = 1; k < kMaxWorld; ++k) d += (k < world && tile_start[k] <= p) ? 1 : 0;
-        const unsigned long long b = base[d];
-        if (b != ~0ull) tg.bucket[d][b + (p - tile_start[d])] = s_keys[p];
+          for (int k = 1; k < kMaxWorld; ++k) d += (k < world && tile_start[k] <= p) ? 1 : 0;
+          const unsigned long long b = base[d];
+          if (b != ~0ull) s_bucket[d][b + (p - tile_start[d])] = s_keys[p];
+        }
       }
     }
     // ---- ticket: last CTA tells every peer that this rank has finished writing
@@ -389,7 +467,12 @@ extern "C" int b200_sort_mgpu_scatter(const void* keys, size_t n_local, int key_
   }
   const int idx_bits = idx_bits_for(world);
   B200_REQUIRE(n_local > 0, "sort_mgpu: empty shards are not supported");
-  const unsigned grid = (phase_mask & 1) ? (unsigned)((n_local + kPartTile - 1) / kPartTile) : 1u;
+  unsigned grid = 1u;
+  if (phase_mask & 1) {
+    const size_t tiles = (n_local + kPartTile - 1) / kPartTile;
+    const size_t resident = (size_t)device_info().sm_count * 2;  // 2 CTAs of 512 threads per SM
+    grid = (unsigned)(tiles < resident ? tiles : resident);
+  }
   cudaStream_t st = as_stream(s);
 #define LAUNCH_PART(KT)                                                                         \
   sort_partition_scatter_kernel<KT><<<grid, kPartThreads, 0, st>>>(                             \

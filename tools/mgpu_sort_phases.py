@@ -34,9 +34,9 @@ def main():
 
     for rep in range(3):
         t1 = timed(lambda: S.mgpu_splitters(m.keys, m.samples, m.ws.ptrs_dev, r, world, g.next_epoch(), 3))
-        t2 = timed(lambda: S.mgpu_count(m.keys, split, m.capacity, m.ws, r, world))
+        t2 = timed(lambda: S.mgpu_count(m.keys, split, m.capacity, m.ws, r, world)) if m.reserve else 0.0
         t3 = timed(lambda: S.mgpu_scatter(m.keys, split, m.sym_bucket.peer_ptrs, None, m.capacity, m.ws, r, world,
-                                          g.next_epoch(), 1 | 2 | 8))
+                                          g.next_epoch(), 1 | 2 | (8 if m.reserve else 0)))
         t4 = timed(lambda: S.sort_devn(m.bucket, m.tmp, ws_local + m._off["sort_recv_count"], m.scratch))
         if r == 0:
             print(f"rep {rep}: splitters {t1:.3f} ms, count+reserve {t2:.3f} ms, scatter {t3:.3f} ms, "
