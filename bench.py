@@ -124,6 +124,8 @@ def run_own(args):
         ms = timed_steps(group, model.step, args.steps, args.warmup)
     launches_timed = (N.launch_count() - launches0) * args.steps // (args.steps + args.warmup)
     clock_summary = clocks.summary()
+    # context: a plain device-to-device copy of the same band (same bytes read + written)
+    copy_ms = timed_steps(group, lambda: model.out.copy_(model.band), 5, 2)
     total_bytes = BYTES_PER_PX * w * h
     value = total_bytes / ms / 1e6
     peak, peak_kind = peak_gbs()
@@ -221,6 +223,9 @@ def run_own(args):
                        "l2_policy": "inputs larger than L2 (>= 2 GiB read + 2 GiB written per GPU per step)"},
             "frac_of_hbm_roofline": round(value / (peak * world), 3), "roofline_peak_gbs_per_gpu": peak,
             "roofline_kind": f"of {peak_kind}",
+            "context": {"torch_copy_same_band_GBps": round(BYTES_PER_PX * w * h / copy_ms / 1e6, 1),
+                        "note": "library copy of the same band, max over ranks; footprints this large copy "
+                                "slower than the 2+2 GiB copy MEASURED_PEAKS.json was taken on"},
             "clocks": {"sm_mhz": clock_summary["sm_mhz"], "sm_max_mhz": clock_summary["sm_max_mhz"],
                        "reasons": clock_summary["reasons"], "samples": clock_summary["samples"]},
             "e2e": e2e, "gpu_launches": int(launches_timed), "labs": labs,

@@ -171,6 +171,25 @@ __device__ __forceinline__ void tma_load_2d(void* smem_dst, const void* tmap, in
       "l"(tmap), "r"(c0), "r"(c1), "r"(smem_u32(bar))
       : "memory");
 }
+// same, with an L2 eviction-priority policy (createpolicy) attached to the fetched lines
+__device__ __forceinline__ void tma_load_2d_hint(void* smem_dst, const void* tmap, int c0, int c1,
+                                                 uint64_t* bar, uint64_t policy) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes"
+      ".L2::cache_hint [%0], [%1, {%2, %3}], [%4], %5;" ::"r"(smem_u32(smem_dst)),
+      "l"(tmap), "r"(c0), "r"(c1), "r"(smem_u32(bar)), "l"(policy)
+      : "memory");
+}
+__device__ __forceinline__ uint64_t l2_policy_evict_first() {
+  uint64_t p;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
+  return p;
+}
+__device__ __forceinline__ uint64_t l2_policy_evict_last() {
+  uint64_t p;
+  asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p));
+  return p;
+}
 // 2-D tiled TMA store shared -> global (bulk async group).
 __device__ __forceinline__ void tma_store_2d(const void* tmap, const void* smem_src, int c0,
                                              int c1) {

@@ -17,6 +17,8 @@ def main():
     dev = torch.device("cuda:0")
     if what.startswith("lab2"):
         h = w = 16384
+        if what.endswith("_big"):          # 4 GiB in + 4 GiB out, the flagship's row pitch
+            h, w, what = 16384, 65536, what[:-4]
         img = torch.randint(-2 ** 31, 2 ** 31 - 1, (h, w), dtype=torch.int32, device=dev)
         out = torch.empty_like(img)
         for _ in range(reps):
