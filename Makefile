@@ -102,7 +102,8 @@ hw2/src/hw2: apps/hw2.c
 # SASS listings for profiles/ (evidence of UTMALDG/UTMASTG, vector widths, ...)
 sass: $(SO)
 	mkdir -p profiles/sass
-	for o in $(CU_OBJS); do cuobjdump -sass $$o > profiles/sass/$$(basename $$o .o).sass; done
+	for o in $(CU_OBJS); do cuobjdump -sass $$o | sed -e 's#/\* 0x[0-9a-f]* \*/##' -e 's/[ \t]*$$//' | grep -v '^$$' \
+	    > profiles/sass/$$(basename $$o .o).sass; done
 
 clean:
 	rm -rf $(BUILD) $(SO) $(CUDA_BINS) $(CPU_BINS)

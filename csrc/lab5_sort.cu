@@ -474,19 +474,17 @@ static int sort32(const uint32_t* input, uint32_t* keys, uint32_t* tmp, size_t n
                   const unsigned long long* n_dev, const SortScratch& sc, cudaStream_t st) {
   const int sms = device_info().sm_count;
   // how many of the 16 keys per thread are matched with ballots (the rest go through
-  // shared memory); tunable: B200LABS_SORT_BALLOT=0|4|8|12|16
+  // shared memory); tunable: B200LABS_SORT_BALLOT=0|8|16
   static const int nm = [] {
     const char* e = getenv("B200LABS_SORT_BALLOT");
     int v = e ? atoi(e) : kMatchItems;
-    return v <= 0 ? 0 : v <= 4 ? 4 : v <= 8 ? 8 : v <= 12 ? 12 : 16;
+    return v <= 0 ? 0 : v <= 8 ? 8 : 16;
   }();
   using Kernel = void (*)(const uint32_t*, uint32_t*, size_t, const unsigned long long*, int,
                           const unsigned long long*, unsigned long long*, uint32_t*);
-  const Kernel kernel = nm == 0    ? sort_onesweep_kernel<KT, 0>
-                        : nm == 4  ? sort_onesweep_kernel<KT, 4>
-                        : nm == 8  ? sort_onesweep_kernel<KT, 8>
-                        : nm == 12 ? sort_onesweep_kernel<KT, 12>
-                                   : sort_onesweep_kernel<KT, 16>;
+  const Kernel kernel = nm == 0   ? sort_onesweep_kernel<KT, 0>
+                        : nm == 8 ? sort_onesweep_kernel<KT, 8>
+                                  : sort_onesweep_kernel<KT, 16>;
   // persistent CTAs with cp.async prefetch of the next tile (B200LABS_SORT_PERSIST=0 disables)
   static const bool persist_env = [] {
     const char* e = getenv("B200LABS_SORT_PERSIST");
