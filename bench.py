@@ -46,7 +46,8 @@ def parse_args():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-extras", action="store_true")
     ap.add_argument("--e2e-steps", type=int, default=None)
-    ap.add_argument("--ref-max-seconds", type=float, default=1500.0)
+    ap.add_argument("--ref-max-seconds", type=float, default=420.0,
+                    help="reference arm: cap on total wall time; steps are reduced (and reported) to fit")
     return ap.parse_args()
 
 
@@ -172,6 +173,14 @@ def run_own(args):
         from cuda_mpi_openmp_b200 import ops
 
         xs, xw = 5, 2
+        # lab1: n = 2^28 doubles in total (6.4 GB moved), sliced over the ranks: no communication
+        from cuda_mpi_openmp_b200.parallel import ShardedVectorSub
+        n1 = 1 << 28
+        m1 = ShardedVectorSub(group, n1)
+        t = timed_steps(group, m1.step, 20, 3)
+        labs["lab1_vecsub_n2^28"] = {"ms": round(t, 4), "GBps": round(24 * n1 / t / 1e6, 1),
+                                     "frac_hbm": round(24 * n1 / t / 1e6 / peak / world, 3)}
+        del m1
         if world == 1:
             n = 1 << 25
             a = torch.randn(n, dtype=torch.float64, device=dev)

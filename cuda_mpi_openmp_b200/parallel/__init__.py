@@ -8,9 +8,9 @@ the exchange done by NCCL collectives through torch.distributed.
 """
 from .symm import (PeerGroup, DistPeerGroup, LocalPeerGroup, SoloPeerGroup, SymmetricBuffer,
                    init_distributed)
-from .sharded import ShardedRoberts, ShardedClassifier, ShardedSort, shard_rows
+from .sharded import ShardedVectorSub, ShardedRoberts, ShardedClassifier, ShardedSort, shard_rows
 
 __all__ = [
     "PeerGroup", "DistPeerGroup", "LocalPeerGroup", "SoloPeerGroup", "SymmetricBuffer", "init_distributed",
-    "ShardedRoberts", "ShardedClassifier", "ShardedSort", "shard_rows",
+    "ShardedVectorSub", "ShardedRoberts", "ShardedClassifier", "ShardedSort", "shard_rows",
 ]

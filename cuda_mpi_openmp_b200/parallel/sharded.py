@@ -67,6 +67,26 @@ def _ptr_array(values: Sequence[int]):
     return arr
 
 
+# ------------------------------------------------------------------------- lab1
+class ShardedVectorSub:
+    """lab1 over several GPUs: pure data parallelism — every rank subtracts its slice,
+    nothing is exchanged (ref: lab1/src/main.cu:22-29 is a single-GPU grid-stride loop)."""
+
+    def __init__(self, group: PeerGroup, n_total: int):
+        from ..ops.vecsub import vecsub
+        self._op = vecsub
+        lo, hi = shard_rows(n_total, group.world)[group.rank]
+        self.lo, self.hi = lo, hi
+        dev = group.device
+        self.a = torch.randn(hi - lo, dtype=torch.float64, device=dev)
+        self.b = torch.randn(hi - lo, dtype=torch.float64, device=dev)
+        self.c = torch.empty_like(self.a)
+        self.launches_per_step = 1
+
+    def step(self) -> torch.Tensor:
+        return self._op(self.a, self.b, self.c)
+
+
 # ------------------------------------------------------------------------- lab2
 class ShardedRoberts:
     """Row-sharded Roberts filter.  The band lives in a symmetric buffer so that rank

@@ -151,3 +151,35 @@ def test_sample_sort_fused_scatter(cuda_device, world, dtype, kind):
     assert np.array_equal(got, np.sort(np.concatenate(shards)))
     for b in buckets:
         b.free()
+
+
+def test_bucket_overflow_is_detected_not_fatal(cuda_device):
+    """A destination bucket that is too small must raise the sticky error word and drop
+    the excess keys — never write out of bounds, never hang."""
+    world, n_local = 2, 50_000
+    rng = np.random.default_rng(77)
+    group = LocalPeerGroup(world, cuda_device)
+    ws = group.workspaces()
+    capacity = 20_000                                   # deliberately far too small
+    buckets = group.alloc((capacity + 64) * 4)
+    guard = 0x5A5A5A5A
+    for b in buckets:
+        b.view(torch.int32, capacity + 64)[capacity:] = guard
+    d_keys = [torch.from_numpy(rng.integers(-2**31, 2**31 - 1, n_local, dtype=np.int64).astype(np.int32)).to(cuda_device)
+              for _ in range(world)]
+    off = {k: group.ranks[0].ws_offset(k) for k in ("sort_splitters", "sort_recv_count", "error")}
+    e1, e2 = group.next_epoch(), group.next_epoch()
+    for phase in (1, 2):
+        for r in range(world):
+            S.mgpu_splitters(d_keys[r], S.samples_per_rank_for(world), ws[r].ptrs_dev, r, world, e1, phase)
+    for phase in (1, 2):
+        for r in range(world):
+            S.mgpu_scatter(d_keys[r], ws[r].local_ptr + off["sort_splitters"], buckets[r].peer_ptrs, None, capacity,
+                           ws[r], r, world, e2, phase)
+    torch.cuda.synchronize()
+    errors = [int(w_.local[off["error"]:][:8].view(torch.int64).item()) for w_ in ws]
+    assert any(e & 2 for e in errors)                   # kErrSortOverflow
+    for r, b in enumerate(buckets):
+        assert bool((b.view(torch.int32, capacity + 64)[capacity:] == guard).all()), r   # no overrun
+        assert int(ws[r].local[off["sort_recv_count"]:][:8].view(torch.int64).item()) <= capacity
+        b.free()
