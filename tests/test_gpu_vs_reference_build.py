@@ -1,0 +1,104 @@
+"""Our CUDA binaries against the UNMODIFIED reference built for sm_100a
+(baseline/_ref/bin, see baseline/install_reference.sh), on the same GPU:
+bit-for-bit output equality on random and real images, and the reference's own
+harness driving our binaries.  Skipped when the reference build is not present."""
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+from cuda_mpi_openmp_b200.utils import ImgData, encode_data_bytes
+
+pytestmark = pytest.mark.gpu
+
+
+def ref_bin(root, name):
+    p = root / "baseline/_ref/bin" / name
+    if not p.exists():
+        pytest.skip("reference build not present (run baseline/install_reference.sh)")
+    return p
+
+
+def run(exe, stdin, env=None):
+    r = subprocess.run([str(exe)], input=stdin, capture_output=True, text=True, timeout=300,
+                       env={**os.environ, **(env or {})})
+    assert r.returncode == 0, r.stderr[-800:]
+    return r.stdout
+
+
+def test_lab2_bit_identical_to_reference_binary(built, cuda_device, tmp_path):
+    ref = ref_bin(built, "lab2_cuda_exe")
+    rng = np.random.default_rng(5)
+    images = {
+        "rand": rng.integers(0, 256, size=(601, 1028, 4), dtype=np.uint8),
+        "odd": rng.integers(0, 256, size=(37, 53, 4), dtype=np.uint8),
+        "world_map": ImgData(str(built / "lab2/test_data/world_map.data"), materialize=False).rgba,
+        "lenna": ImgData(str(built / "lab2/test_data/lenna.data"), materialize=False).rgba,
+    }
+    flat = rng.integers(0, 256, size=(64, 256, 4), dtype=np.uint8)
+    flat[16:48] = flat[16]                      # constant rows: gradient exactly zero
+    images["flat"] = flat
+    for name, img in images.items():
+        src = tmp_path / f"{name}.data"
+        src.write_bytes(encode_data_bytes(img))
+        a, b = tmp_path / f"{name}_ref.data", tmp_path / f"{name}_ours.data"
+        run(ref, f"{src}\n{a}")
+        for variant in ("auto", "generic"):
+            run(built / "lab2/src/cuda_exe", f"{src}\n{b}", env={"B200LABS_ROBERTS": variant})
+            assert a.read_bytes() == b.read_bytes(), (name, variant)
+
+
+def test_lab3_matches_reference_binary(built, cuda_device, tmp_path):
+    ref = ref_bin(built, "lab3_cuda_exe")
+    rng = np.random.default_rng(6)
+    h, w, nc = 240, 320, 7
+    img = rng.integers(0, 256, size=(h, w, 4), dtype=np.uint8)
+    src = tmp_path / "img.data"
+    src.write_bytes(encode_data_bytes(img))
+    spec = f"{nc}\n" + "\n".join(
+        f"60 " + " ".join(f"{x} {y}" for x, y in zip(rng.integers(0, w, 60), rng.integers(0, h, 60)))
+        for _ in range(nc))
+    a, b = tmp_path / "ref.data", tmp_path / "ours.data"
+    run(ref, f"{src}\n{a}\n{spec}")
+    # same two-pass host statistics as the reference -> bit-identical output
+    run(built / "lab3/src/cuda_exe", f"{src}\n{b}\n{spec}", env={"B200LABS_LAB3_STATS": "host"})
+    assert a.read_bytes() == b.read_bytes()
+    # default: exact integer moments on the GPU; parameters differ by rounding only, so at most
+    # a handful of numerically tied pixels may change class
+    run(built / "lab3/src/cuda_exe", f"{src}\n{b}\n{spec}")
+    ra = np.frombuffer(a.read_bytes(), dtype=np.uint8, offset=8)
+    rb = np.frombuffer(b.read_bytes(), dtype=np.uint8, offset=8)
+    assert (ra != rb).sum() <= 3
+
+
+def test_lab1_matches_reference_binary(built, cuda_device):
+    ref = ref_bin(built, "lab1_cuda_exe")
+    rng = np.random.default_rng(7)
+    n = 1500
+    a, b = rng.uniform(-1e100, 1e100, n), rng.uniform(-1e100, 1e100, n)
+    stdin = f"{n}\n" + " ".join(f"{v:.10e}" for v in a) + "\n" + " ".join(f"{v:.10e}" for v in b)
+    assert run(ref, stdin) == run(built / "lab1/src/cuda_exe", stdin)
+
+
+def test_gpu_info_matches_reference_binary(built, cuda_device):
+    ref = ref_bin(built, "gpu_info")
+    assert run(ref, "") == run(built / "gpu_info/src/gpu_info", "")
+
+
+def test_reference_harness_drives_our_cuda_binary(built, cuda_device):
+    if not (built / "baseline/_ref/src/run_test.py").exists():
+        pytest.skip("reference tree not present")
+    before = {p.name for p in (built / "lab2/data").iterdir()}
+    cmd = [sys.executable, "tools/run_reference_harness.py", "--binary_path_cuda", "./lab2/src/to_plot_cuda_exe",
+           "--k_times", "7", "--kernel_sizes", "[[[32, 32], [16, 16]], [[16, 16], [32, 32]]]",
+           "--metadata_columns2plot", '["filename"]']
+    r = subprocess.run(cmd, cwd=built, capture_output=True, text=True, timeout=900)
+    for p in (built / "lab2/data").iterdir():
+        if p.name not in before:
+            p.unlink()
+    for p in (built / "lab2/data_out_gt").iterdir():
+        if p.suffix in (".data", ".png"):
+            p.unlink()
+    assert r.returncode == 0 and "SUCCESS!" in r.stdout and "FAILED" not in r.stdout, r.stdout[-1500:] + r.stderr[-1500:]
