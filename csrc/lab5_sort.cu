@@ -35,12 +35,12 @@ constexpr int kTile = kSortThreads * kItems;  // 8192 keys
 #ifndef B200_SORT_PERSIST_DEFAULT
 #define B200_SORT_PERSIST_DEFAULT 0
 #endif
-#ifndef B200_SORT_MATCH_ITEMS
-#define B200_SORT_MATCH_ITEMS 0
+#ifndef B200_SORT_BALLOT_ITEMS
+#define B200_SORT_BALLOT_ITEMS 0
 #endif
 // how many of a thread's 16 keys find their same-digit lanes with ballots; the rest
 // use shared-memory OR words (see sweep_tile)
-constexpr int kMatchItems = B200_SORT_MATCH_ITEMS;
+constexpr int kBallotItems = B200_SORT_BALLOT_ITEMS;
 
 // order-preserving bijection key bits -> unsigned
 template <int KT>
@@ -477,7 +477,7 @@ static int sort32(const uint32_t* input, uint32_t* keys, uint32_t* tmp, size_t n
   // shared memory); tunable: B200LABS_SORT_BALLOT=0|8|16
   static const int nm = [] {
     const char* e = getenv("B200LABS_SORT_BALLOT");
-    int v = e ? atoi(e) : kMatchItems;
+    int v = e ? atoi(e) : kBallotItems;
     return v <= 0 ? 0 : v <= 8 ? 8 : 16;
   }();
   using Kernel = void (*)(const uint32_t*, uint32_t*, size_t, const unsigned long long*, int,
