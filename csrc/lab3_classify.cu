@@ -15,6 +15,7 @@
 //    table that lives in the 126 MB L2, then the image pass is a byte gather at
 //    HBM speed.  Decisions are bit-identical to DIRECT by construction.
 #include <cfloat>
+#include <cstdlib>
 
 #include "common.cuh"
 #include "lab3_math.cuh"
@@ -123,6 +124,15 @@ __global__ void __launch_bounds__(kClsThreads)
             ((uint32_t)(best[2] & 0xff) << 16) | ((uint32_t)(best[3] & 0xff) << 24);
 }
 
+// LUT build, hoisted form (see lut_build_block): one CTA per (G, 64 R values), all B
+__global__ void __launch_bounds__(kLutThreads)
+    lab3_lut_build_hoisted_kernel(uint8_t* __restrict__ lut, int nc, const double* __restrict__ params) {
+  extern __shared__ __align__(16) uint8_t lut_smem_raw[];
+  LutSmem& S = *reinterpret_cast<LutSmem*>(lut_smem_raw);
+  const int g = blockIdx.x >> 2, r0 = (blockIdx.x & 3) * kLutR;
+  lut_build_block(S, nc, params, g, r0, 0, 256, [&](uint32_t id, uint8_t cls) { lut[id] = cls; });
+}
+
 // LUT apply: 4 px per thread, byte gathers through the read-only path
 __global__ void __launch_bounds__(kClsThreads)
     lab3_lut_apply_kernel(uint32_t* __restrict__ img, int64_t n_vec,
@@ -210,8 +220,26 @@ extern "C" int b200_lab3_classify(void* img, int64_t npix, int nc, const double*
   if (variant == B200_CLASSIFY_LUT) {
     B200_REQUIRE(scratch_bytes >= kLutBytes, "lab3: LUT variant needs %zu bytes of scratch",
                  kLutBytes);
-    lab3_lut_build_kernel<<<(1 << 22) / kClsThreads, kClsThreads, 0, st>>>((uint32_t*)scratch, nc,
-                                                                           params);
+    static const bool plain_build = [] {
+      const char* e = getenv("B200LABS_LAB3_LUT_BUILD");
+      return e && !strcmp(e, "plain");
+    }();
+    if (plain_build) {
+      lab3_lut_build_kernel<<<(1 << 22) / kClsThreads, kClsThreads, 0, st>>>((uint32_t*)scratch, nc,
+                                                                             params);
+    } else {
+      static bool attr_set[64] = {false};
+      int dev = 0;
+      cudaGetDevice(&dev);
+      if (!attr_set[dev & 63]) {
+        B200_CUDA_OK(cudaFuncSetAttribute(lab3_lut_build_hoisted_kernel,
+                                          cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          (int)sizeof(LutSmem)));
+        attr_set[dev & 63] = true;
+      }
+      lab3_lut_build_hoisted_kernel<<<256 * (256 / kLutR), kLutThreads, sizeof(LutSmem), st>>>(
+          (uint8_t*)scratch, nc, params);
+    }
     B200_LAUNCH_OK();
     if (n_vec) {
       lab3_lut_apply_kernel<<<grid_for(n_vec, 8), kClsThreads, 0, st>>>((uint32_t*)img, n_vec,

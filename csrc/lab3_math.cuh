@@ -93,4 +93,68 @@ __device__ __forceinline__ void load_params_smem(double* sp, const double* param
 }
 
 
+// ---- colour-table builder with the class-invariant part of the chain hoisted ----
+// For a fixed (R, G) the two inner FMAs of every temp[k] do not depend on B:
+//   u_k = fma(d1, m[1][k], fma(d0, m[0][k], 0))           (6 FMA + 2 subtractions)
+// so a CTA computes u_k once per (class, R) for its G, keeps them in shared memory,
+// and each colour then costs d2 = B - mu2, temp[k] = fma(d2, m[2][k], u_k) and the
+// three-FMA distance: 7 fp64 operations + compare instead of 16 — the SAME operation
+// sequence per colour as maha(), hence bit-identical decisions.
+constexpr int kLutR = 64;        // R values per CTA
+constexpr int kLutBGroup = 8;    // B values per thread task
+constexpr int kLutThreads = 256;
+struct LutSmem {
+  double u[kMaxC][3][kLutR];
+  double d0[kMaxC][kLutR];
+  double d1[kMaxC];
+  double sp[kMaxC * kNP];
+};
+
+// Classifies the colours {R in [r0, r0+64), G = g, B in [b_begin, b_end)} (b range a
+// multiple of 8) and hands every (colour id, class) to `emit`.
+template <typename Emit>
+__device__ __forceinline__ void lut_build_block(LutSmem& S, int nc, const double* __restrict__ params,
+                                                int g, int r0, int b_begin, int b_end, Emit emit) {
+  const int tid = threadIdx.x;
+  for (int i = tid; i < nc * kNP; i += kLutThreads) S.sp[i] = params[i];
+  __syncthreads();
+  for (int i = tid; i < nc * kLutR; i += kLutThreads) {
+    const int c = i / kLutR, r = i - c * kLutR;
+    const double* p = S.sp + c * kNP;
+    const double d0 = __dsub_rn((double)(r0 + r), p[0]);
+    const double d1 = __dsub_rn((double)g, p[1]);
+    S.d0[c][r] = d0;
+    if (r == 0) S.d1[c] = d1;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) S.u[c][k][r] = __fma_rn(d1, p[6 + k], __fma_rn(d0, p[3 + k], 0.0));
+  }
+  __syncthreads();
+  const int n_groups = (b_end - b_begin) / kLutBGroup;
+  for (int t = tid; t < n_groups * kLutR; t += kLutThreads) {
+    const int r = t & (kLutR - 1), b0 = b_begin + (t / kLutR) * kLutBGroup;
+    double mind[kLutBGroup];
+    int best[kLutBGroup];
+#pragma unroll
+    for (int j = 0; j < kLutBGroup; ++j) mind[j] = DBL_MAX, best[j] = -1;
+    for (int c = 0; c < nc; ++c) {
+      const double* p = S.sp + c * kNP;
+      const double u0 = S.u[c][0][r], u1 = S.u[c][1][r], u2 = S.u[c][2][r];
+      const double d0 = S.d0[c][r], d1 = S.d1[c];
+      const double mu2 = p[2], m20 = p[9], m21 = p[10], m22 = p[11];
+#pragma unroll
+      for (int j = 0; j < kLutBGroup; ++j) {
+        const double d2 = __dsub_rn((double)(b0 + j), mu2);
+        const double t0 = __fma_rn(d2, m20, u0), t1 = __fma_rn(d2, m21, u1), t2 = __fma_rn(d2, m22, u2);
+        double dist = __fma_rn(d0, t0, 0.0);
+        dist = __fma_rn(d1, t1, dist);
+        dist = __fma_rn(d2, t2, dist);
+        if (dist < mind[j]) mind[j] = dist, best[j] = c;
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < kLutBGroup; ++j)
+      emit(((uint32_t)(b0 + j) << 16) | ((uint32_t)g << 8) | (uint32_t)(r0 + r), (uint8_t)best[j]);
+  }
+}
+
 }  // namespace b200

@@ -116,35 +116,36 @@ __global__ void __launch_bounds__(kStatThreads)
 }
 
 // ---- colour table built cooperatively: 1/world of the 2^24 colours per rank ----
-// Each rank classifies its slice of the colour cube with the usual DFMA chain and
-// stores the packed class bytes into EVERY rank's table (remote 128-byte-per-warp
-// stores), so the table build scales with the GPU count instead of being repeated
-// on every GPU; the last CTA fences, signals all peers and waits for them, after
-// which the local table is complete and the image pass can gather from it.
-constexpr int kLutThreads = 256;
-
+// Each rank classifies its slice of the colour cube (a range of B values) and stores
+// the class bytes into EVERY rank's table over NVLink, so the table build scales with
+// the GPU count instead of being repeated on every GPU; the last CTA fences, signals
+// all peers and waits for them, after which the local table is complete and the image
+// pass can gather from it.
 struct LutTargets {
-  uint32_t* lut4[kMaxWorld];  // every rank's table, peer-mapped, as packed uint32
+  uint8_t* lut[kMaxWorld];  // every rank's table, peer-mapped
 };
 
+// Rank r classifies the colours with B in [r*256/world, (r+1)*256/world) — one CTA
+// per (G, 64 R values), hoisted chain as in lut_build_block — and stores every class
+// byte into all tables (a warp writes 32 consecutive bytes = one sector per table).
 __global__ void __launch_bounds__(kLutThreads)
     lab3_lut_build_allgather_kernel(LutTargets tg, int nc, const double* __restrict__ params,
                                     SymmPeers peers, int rank, int world, uint64_t epoch,
                                     int phase_mask, unsigned long long timeout_ns) {
-  __shared__ double sp[kMaxC * kNP];
+  extern __shared__ __align__(16) uint8_t lut_smem_raw[];
+  LutSmem& S = *reinterpret_cast<LutSmem*>(lut_smem_raw);
+  __shared__ uint8_t* s_lut[kMaxWorld];
   __shared__ bool is_last;
   SymmWorkspace* me = peers.ws[rank];
   const int tid = threadIdx.x;
   if (phase_mask & 1) {
-    load_params_smem(sp, params, nc);
-    const uint32_t per_rank = (1u << 22) / world;  // packed words per rank
-    const uint32_t t = rank * per_rank + blockIdx.x * kLutThreads + tid;
-    uint32_t px[4] = {4 * t, 4 * t + 1, 4 * t + 2, 4 * t + 3};
-    int best[4];
-    classify_group<4>(px, nc, sp, best);
-    const uint32_t word = (uint32_t)(best[0] & 0xff) | ((uint32_t)(best[1] & 0xff) << 8) |
-                          ((uint32_t)(best[2] & 0xff) << 16) | ((uint32_t)(best[3] & 0xff) << 24);
-    for (int p = 0; p < world; ++p) tg.lut4[(rank + p) % world][t] = word;  // own copy first
+    if (tid < kMaxWorld) s_lut[tid] = tid < world ? tg.lut[(rank + tid) % world] : nullptr;  // own copy first
+    const int per_rank = 256 / world;
+    const int g = blockIdx.x >> 2, r0 = (blockIdx.x & 3) * kLutR;
+    lut_build_block(S, nc, params, g, r0, rank * per_rank, (rank + 1) * per_rank,
+                    [&](uint32_t id, uint8_t cls) {
+                      for (int p = 0; p < world; ++p) s_lut[p][id] = cls;
+                    });
     __threadfence_system();
     __syncthreads();
     if (tid == 0) is_last = atomicAdd(&me->lab3_lut_blocks_done, 1u) == gridDim.x - 1;
@@ -175,10 +176,19 @@ extern "C" int b200_lab3_lut_build_allgather(void* const* lut_ptrs, int nc, cons
                "lab3: lut all-gather needs a power-of-two world <= %d (rank %d, world %d)",
                kMaxWorld, rank, world);
   LutTargets tg;
-  for (int p = 0; p < kMaxWorld; ++p) tg.lut4[p] = p < world ? (uint32_t*)lut_ptrs[p] : nullptr;
+  for (int p = 0; p < kMaxWorld; ++p) tg.lut[p] = p < world ? (uint8_t*)lut_ptrs[p] : nullptr;
   SymmPeers peers{(SymmWorkspace* const*)ws_ptrs};
-  const unsigned grid = (phase_mask & 1) ? ((1u << 22) / world) / kLutThreads : 1u;
-  lab3_lut_build_allgather_kernel<<<grid, kLutThreads, 0, as_stream(s)>>>(
+  B200_REQUIRE((256 / world) % kLutBGroup == 0, "lab3: world %d leaves fewer than 8 B values per rank", world);
+  static bool attr_set[64] = {false};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (!attr_set[dev & 63]) {
+    B200_CUDA_OK(cudaFuncSetAttribute(lab3_lut_build_allgather_kernel,
+                                      cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(LutSmem)));
+    attr_set[dev & 63] = true;
+  }
+  const unsigned grid = (phase_mask & 1) ? 256u * (256 / kLutR) : 1u;
+  lab3_lut_build_allgather_kernel<<<grid, kLutThreads, sizeof(LutSmem), as_stream(s)>>>(
       tg, nc, params, peers, rank, world, epoch, phase_mask, kDefaultTimeoutNs);
   B200_LAUNCH_OK();
   return 0;
