@@ -133,6 +133,18 @@ __global__ void __launch_bounds__(kLutThreads)
   lut_build_block(S, nc, params, g, r0, 0, 256, [&](uint32_t id, uint8_t cls) { lut[id] = cls; });
 }
 
+__device__ __forceinline__ uint32_t lut_gather(const uint8_t* p) {
+#ifdef B200_LUT_GATHER_LDG
+  return __ldg(p);
+#else
+  // the 16 MiB table lives in L2; a random colour practically never hits the 256 KB L1,
+  // so do not allocate the line there
+  uint32_t v;
+  asm volatile("ld.global.nc.L1::no_allocate.u8 %0, [%1];" : "=r"(v) : "l"(p));
+  return v;
+#endif
+}
+
 // LUT apply: 4 px per thread, byte gathers through the read-only path
 __global__ void __launch_bounds__(kClsThreads)
     lab3_lut_apply_kernel(uint32_t* __restrict__ img, int64_t n_vec,
@@ -140,8 +152,8 @@ __global__ void __launch_bounds__(kClsThreads)
   const int64_t stride = (int64_t)gridDim.x * kClsThreads;
   for (int64_t i = (int64_t)blockIdx.x * kClsThreads + threadIdx.x; i < n_vec; i += stride) {
     uint4 v = ld_stream_u4(img + 4 * i);
-    const uint32_t c0 = __ldg(lut + (v.x & 0xffffffu)), c1 = __ldg(lut + (v.y & 0xffffffu)),
-                   c2 = __ldg(lut + (v.z & 0xffffffu)), c3 = __ldg(lut + (v.w & 0xffffffu));
+    const uint32_t c0 = lut_gather(lut + (v.x & 0xffffffu)), c1 = lut_gather(lut + (v.y & 0xffffffu)),
+                   c2 = lut_gather(lut + (v.z & 0xffffffu)), c3 = lut_gather(lut + (v.w & 0xffffffu));
     v.x = (v.x & 0xffffffu) | (c0 << 24);
     v.y = (v.y & 0xffffffu) | (c1 << 24);
     v.z = (v.z & 0xffffffu) | (c2 << 24);
