@@ -33,13 +33,16 @@ __global__ void __launch_bounds__(kStatThreads)
                                 const int* __restrict__ class_off, int nc, SymmPeers peers,
                                 int rank, int world, uint64_t epoch, double* __restrict__ params,
                                 long long* __restrict__ moments_out, int phase_mask,
-                                unsigned long long timeout_ns) {
+                                unsigned long long timeout_ns,
+                                unsigned long long* __restrict__ mc_acc /* NVLS multicast view */,
+                                long long* __restrict__ local_acc /* this GPU's copy of it */,
+                                int par_override /* >= 0: accumulator half to use */) {
   SymmWorkspace* me = peers.ws[rank];
   __shared__ unsigned long long red[kStatThreads / 32][kLab3M];
   __shared__ long long total[kLab3C][kLab3M];
   __shared__ bool is_last;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int par = (int)(epoch & 1);
+  const int par = par_override >= 0 ? par_override : (int)(epoch & 1);
 
   if (phase_mask & 1) {
     // ---- accumulate this CTA's share of class blockIdx.y --------------------
@@ -84,12 +87,32 @@ __global__ void __launch_bounds__(kStatThreads)
     __syncthreads();
     if (!is_last) return;
     __threadfence();
-    // ---- push my partial sums into every peer's slot (remote stores) ---------
-    for (int i = tid; i < nc * kLab3M; i += kStatThreads) {
-      long long* acc = &me->lab3_acc[0][0] + i;
-      const long long v = ld_cg_s64(acc);
-      *acc = 0;  // ready for the next call
-      for (int p = 0; p < world; ++p) (&peers.ws[p]->lab3_slots[par][rank][0][0])[i] = v;
+    if (mc_acc) {
+      // ---- NVLS: one multimem.red per value adds my partial sum into EVERY GPU's copy
+      // of the accumulator (the NVSwitch performs the broadcast-reduction).  The other
+      // parity's accumulator is zeroed first: nobody can add to it before passing this
+      // epoch's barrier, which needs the signal sent below.
+      for (int i = tid; i < kLab3C * kLab3M; i += kStatThreads) local_acc[(par ^ 1) * kLab3C * kLab3M + i] = 0;
+      __threadfence_system();
+      __syncthreads();
+      for (int i = tid; i < nc * kLab3M; i += kStatThreads) {
+        long long* acc = &me->lab3_acc[0][0] + i;
+        const long long v = ld_cg_s64(acc);
+        *acc = 0;
+        if (v)
+          asm volatile("multimem.red.relaxed.sys.global.add.u64 [%0], %1;" ::"l"(
+                           mc_acc + par * kLab3C * kLab3M + i),
+                       "l"(v)
+                       : "memory");
+      }
+    } else {
+      // ---- push my partial sums into every peer's slot (remote stores) ---------
+      for (int i = tid; i < nc * kLab3M; i += kStatThreads) {
+        long long* acc = &me->lab3_acc[0][0] + i;
+        const long long v = ld_cg_s64(acc);
+        *acc = 0;  // ready for the next call
+        for (int p = 0; p < world; ++p) (&peers.ws[p]->lab3_slots[par][rank][0][0])[i] = v;
+      }
     }
     if (tid == 0) me->lab3_blocks_done = 0;
     __threadfence_system();
@@ -106,7 +129,11 @@ __global__ void __launch_bounds__(kStatThreads)
     __syncthreads();
     for (int i = tid; i < nc * kLab3M; i += kStatThreads) {
       long long s = 0;
-      for (int p = 0; p < world; ++p) s += ld_cg_s64(&me->lab3_slots[par][p][0][0] + i);
+      if (local_acc) {
+        s = ld_cg_s64(local_acc + par * kLab3C * kLab3M + i);  // already reduced by the switch
+      } else {
+        for (int p = 0; p < world; ++p) s += ld_cg_s64(&me->lab3_slots[par][p][0][0] + i);
+      }
       (&total[0][0])[i] = s;
       if (moments_out) moments_out[i] = s;
     }
@@ -210,7 +237,33 @@ extern "C" int b200_lab3_stats_allreduce(const void* img, int w, int64_t y0, int
   dim3 grid = (phase_mask & 1) ? dim3(64, nc) : dim3(1, 1);
   lab3_stats_allreduce_kernel<<<grid, kStatThreads, 0, as_stream(s)>>>(
       (const uint32_t*)img, w, y0, h_local, (const int2*)pts, class_off, nc, peers, rank, world,
-      epoch, params, moments_out, phase_mask, kDefaultTimeoutNs);
+      epoch, params, moments_out, phase_mask, kDefaultTimeoutNs, nullptr, nullptr, -1);
+  B200_LAUNCH_OK();
+  return 0;
+}
+
+// Same, with the all-reduce done by NVLS: `mc_acc` is the MULTICAST address of a
+// symmetric int64[2][32][10] accumulator (zero-initialised, e.g. from
+// torch.distributed._symmetric_memory), `local_acc` this GPU's unicast address of the
+// same buffer.  Every rank adds its partial sums with multimem.red — the NVSwitch
+// applies them to all GPUs' copies — then the usual flag barrier, and each rank reads
+// its own copy.  The two halves of the accumulator alternate: `call_parity` must flip
+// on every call (identically on all ranks); the half not in use is zeroed by the call.
+// Product path only (no phase split): it needs real NVLS hardware.
+extern "C" int b200_lab3_stats_nvls(const void* img, int w, int64_t y0, int64_t h_local,
+                                    const int* pts, const int* class_off, int nc,
+                                    const void* ws_ptrs, void* mc_acc, void* local_acc, int rank,
+                                    int world, uint64_t epoch, int call_parity, double* params,
+                                    long long* moments_out, b200_stream_t s) {
+  B200_REQUIRE(nc > 0 && nc <= kLab3C, "lab3: class count %d outside 1..%d", nc, kLab3C);
+  B200_REQUIRE(world >= 1 && world <= kMaxWorld && rank >= 0 && rank < world,
+               "lab3: bad rank/world %d/%d", rank, world);
+  B200_REQUIRE(mc_acc && local_acc, "lab3: NVLS path needs the multicast and the local address");
+  SymmPeers peers{(SymmWorkspace* const*)ws_ptrs};
+  lab3_stats_allreduce_kernel<<<dim3(64, nc), kStatThreads, 0, as_stream(s)>>>(
+      (const uint32_t*)img, w, y0, h_local, (const int2*)pts, class_off, nc, peers, rank, world,
+      epoch, params, moments_out, 3, kDefaultTimeoutNs, (unsigned long long*)mc_acc,
+      (long long*)local_acc, call_parity & 1);
   B200_LAUNCH_OK();
   return 0;
 }

@@ -29,6 +29,9 @@ from .symm import PeerGroup, SymmetricBuffer
 N.register("b200_lab3_stats_allreduce", C.c_int,
            [C.c_void_p, C.c_int, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p,
             C.c_int, C.c_int, C.c_uint64, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p])
+N.register("b200_lab3_stats_nvls", C.c_int,
+           [C.c_void_p, C.c_int, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p,
+            C.c_void_p, C.c_int, C.c_int, C.c_uint64, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p])
 N.register("b200_lab3_lut_build_allgather", C.c_int,
            [C.POINTER(C.c_void_p), C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_uint64, C.c_int,
             C.c_void_p])
@@ -163,7 +166,20 @@ class ShardedClassifier:
 
     def __init__(self, group: PeerGroup, w: int, h_total: int, classes, impl: str = "fused",
                  variant: str = "auto"):
-        assert impl in ("fused", "nccl")
+        # impl "nvls": as "fused", but the statistics are all-reduced by the NVSwitch
+        # (multimem.red on a multicast address obtained from torch's symmetric memory)
+        assert impl in ("fused", "nccl", "nvls")
+        self.nvls = impl == "nvls"
+        if self.nvls:
+            impl = "fused"
+            import torch.distributed._symmetric_memory as symm_mem
+            self._acc = symm_mem.empty(2 * 32 * 10, dtype=torch.int64, device=group.device)
+            self._acc.zero_()
+            self._nvls_calls = 0
+            self._acc_hdl = symm_mem.rendezvous(self._acc, group.pg if group.pg is not None else group.dist.group.WORLD)
+            if not getattr(self._acc_hdl, "multicast_ptr", 0):
+                raise RuntimeError("NVLS multicast is not available on this system")
+            group.barrier()
         self.group, self.w, self.h_total, self.impl, self.variant = group, w, h_total, impl, variant
         self.y0, self.y1 = shard_rows(h_total, group.world)[group.rank]
         self.h_local = self.y1 - self.y0
@@ -187,7 +203,14 @@ class ShardedClassifier:
 
     def fit(self) -> torch.Tensor:
         g = self.group
-        if self.impl == "fused":
+        if self.nvls:
+            N.check(N.lib().b200_lab3_stats_nvls(
+                N.ptr(self.band), self.w, self.y0, self.h_local, N.ptr(self.d_pts), N.ptr(self.d_off), self.nc,
+                N.ptr(self.ws.ptrs_dev), C.c_void_p(self._acc_hdl.multicast_ptr), N.ptr(self._acc), g.rank,
+                g.world, g.next_epoch(), self._nvls_calls & 1, N.ptr(self.params), N.ptr(self.moments),
+                N.current_stream_ptr()), "b200_lab3_stats_nvls")
+            self._nvls_calls += 1
+        elif self.impl == "fused":
             fused_stats(self.band, self.w, self.y0, self.h_local, self.d_pts, self.d_off, self.nc,
                         self.ws.ptrs_dev, g.rank, g.world, g.next_epoch(), self.params, self.moments, 3)
         else:

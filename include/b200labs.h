@@ -167,6 +167,16 @@ int b200_lab3_stats_allreduce(const void* img, int w, int64_t y0, int64_t h_loca
                               double* params, long long* moments_out, int phase_mask,
                               b200_stream_t s);
 
+/* As above, but the sums are all-reduced by NVLS: every rank issues multimem.red on the
+ * multicast address `mc_acc` of a symmetric, zero-initialised int64[2][32][10] buffer
+ * (in-switch reduction lands in every GPU's copy); `local_acc` is this GPU's own
+ * address of the same buffer; call_parity flips on every call.  Needs NVSwitch multicast (e.g. buffers from
+ * torch.distributed._symmetric_memory). */
+int b200_lab3_stats_nvls(const void* img, int w, int64_t y0, int64_t h_local, const int* pts,
+                         const int* class_off, int nc, const void* ws_ptrs, void* mc_acc,
+                         void* local_acc, int rank, int world, uint64_t epoch, int call_parity,
+                         double* params, long long* moments_out, b200_stream_t s);
+
 /* lab3 colour table built cooperatively: each rank classifies 1/world of the 2^24
  * colours and stores the class bytes into every rank's 16 MiB table (lut_ptrs: HOST
  * array [world] of peer-mapped tables); then the image pass against the finished

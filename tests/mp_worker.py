@@ -33,9 +33,16 @@ def main():
     classes = [np.stack([rng.integers(0, w, 500), rng.integers(0, h, 500)], axis=1) for _ in range(nc)]
     p_want = MahalanobisClassifier.reference_params(img, classes, mode="moments")
     c_want = MahalanobisClassifier.reference_classify(img, p_want)
-    for impl, variant in (("fused", "auto"), ("nccl", "auto"), ("fused", "lut"), ("nccl", "lut")):
-        m = ShardedClassifier(g, w, h, classes, impl=impl, variant=variant)
-        assert m.coop_lut == (impl == "fused" and variant == "lut")
+    for impl, variant in (("fused", "auto"), ("nccl", "auto"), ("fused", "lut"), ("nccl", "lut"), ("nvls", "lut")):
+        try:
+            m = ShardedClassifier(g, w, h, classes, impl=impl, variant=variant)
+        except Exception as exc:  # noqa: BLE001 - NVLS needs NVSwitch multicast + torch symmetric memory
+            if impl != "nvls":
+                raise
+            if rank == 0:
+                print("NVLS path skipped:", type(exc).__name__, exc)
+            continue
+        assert m.coop_lut == (impl in ("fused", "nvls") and variant == "lut")
         for rep in range(3):
             m.band.copy_(torch.from_numpy(img[m.y0:m.y1].copy()).view(torch.int32).reshape(m.h_local, w))
             g.barrier()
@@ -44,6 +51,8 @@ def main():
             got = out.cpu().numpy().view(np.uint8).reshape(m.h_local, w, 4)
             assert np.array_equal(got, c_want[m.y0:m.y1]), f"lab3 classify {impl}/{variant} rank {rank}"
         assert g.ws_error() == 0
+        if impl == "nvls" and rank == 0:
+            print("NVLS_STATS_OK (multimem.red all-reduce, bit-identical parameters)")
         g.barrier()
         m.free()
 
