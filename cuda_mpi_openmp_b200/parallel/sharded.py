@@ -167,19 +167,19 @@ class ShardedClassifier:
     def __init__(self, group: PeerGroup, w: int, h_total: int, classes, impl: str = "fused",
                  variant: str = "auto"):
         # impl "nvls": as "fused", but the statistics are all-reduced by the NVSwitch
-        # (multimem.red on a multicast address obtained from torch's symmetric memory)
+        # (multimem.red on the multicast address of a parallel/vmm.py buffer)
         assert impl in ("fused", "nccl", "nvls")
         self.nvls = impl == "nvls"
+        self._acc_buf = None
         if self.nvls:
+            from . import vmm
             impl = "fused"
-            import torch.distributed._symmetric_memory as symm_mem
-            self._acc = symm_mem.empty(2 * 32 * 10, dtype=torch.int64, device=group.device)
-            self._acc.zero_()
-            self._nvls_calls = 0
-            self._acc_hdl = symm_mem.rendezvous(self._acc, group.pg if group.pg is not None else group.dist.group.WORLD)
-            if not getattr(self._acc_hdl, "multicast_ptr", 0):
+            self._acc_buf = vmm.alloc(group, 2 * 32 * 10 * 8, multicast=True, map_peers=False)
+            if not self._acc_buf.mc_ptr:
+                self._acc_buf.free()
                 raise RuntimeError("NVLS multicast is not available on this system")
-            group.barrier()
+            self._acc = self._acc_buf.view(torch.int64, 2 * 32 * 10)
+            self._nvls_calls = 0
         self.group, self.w, self.h_total, self.impl, self.variant = group, w, h_total, impl, variant
         self.y0, self.y1 = shard_rows(h_total, group.world)[group.rank]
         self.h_local = self.y1 - self.y0
@@ -206,7 +206,7 @@ class ShardedClassifier:
         if self.nvls:
             N.check(N.lib().b200_lab3_stats_nvls(
                 N.ptr(self.band), self.w, self.y0, self.h_local, N.ptr(self.d_pts), N.ptr(self.d_off), self.nc,
-                N.ptr(self.ws.ptrs_dev), C.c_void_p(self._acc_hdl.multicast_ptr), N.ptr(self._acc), g.rank,
+                N.ptr(self.ws.ptrs_dev), C.c_void_p(self._acc_buf.mc_ptr), N.ptr(self._acc), g.rank,
                 g.world, g.next_epoch(), self._nvls_calls & 1, N.ptr(self.params), N.ptr(self.moments),
                 N.current_stream_ptr()), "b200_lab3_stats_nvls")
             self._nvls_calls += 1
@@ -233,6 +233,10 @@ class ShardedClassifier:
         if self.sym_lut is not None:
             self.sym_lut.free()
             self.sym_lut = None
+        if self._acc_buf is not None:
+            self._acc = None
+            self._acc_buf.free()
+            self._acc_buf = None
 
 
 # ------------------------------------------------------------------------- lab5

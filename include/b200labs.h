@@ -151,6 +151,36 @@ int b200_enable_peer_access(int peer);
  * "sort_recv_count", "sort_samples", "flags"). */
 size_t b200_symm_workspace_bytes(void);
 size_t b200_symm_offset(const char* field);
+
+/* ---- VMM + NVSwitch multicast runtime (csrc/vmm.cu; no counterpart in the reference) ------
+ * Physical memory from cuMemCreate, shareable between processes as a POSIX file descriptor,
+ * and multicast objects (NVLS): one multimem.* instruction on the multicast address reaches
+ * every bound GPU's copy.  Sequence for a multicast buffer over `world` ranks:
+ *   granularity(world) -> create -> map (local address) -> [rank 0] mc_create + export_fd ->
+ *   fds to the peers (unix socket, SCM_RIGHTS) -> import_fd -> EVERY rank mc_add_device ->
+ *   process barrier -> mc_bind(own handle) -> process barrier -> map(mc handle). */
+int b200_vmm_query(int* vmm_supported, int* multicast_supported);
+int b200_vmm_granularity(int world, size_t* gran_out);
+int b200_vmm_create(size_t bytes, uint64_t* handle_out);
+int b200_vmm_release(uint64_t handle);
+int b200_vmm_export_fd(uint64_t handle, int* fd_out);
+int b200_vmm_import_fd(int fd, uint64_t* handle_out);
+int b200_vmm_map(uint64_t handle, size_t bytes, void** va_out);
+int b200_vmm_unmap(void* va, size_t bytes);
+int b200_mc_create(int num_devices, size_t bytes, uint64_t* mc_out);
+int b200_mc_add_device(uint64_t mc);
+int b200_mc_bind(uint64_t mc, uint64_t mem_handle, size_t bytes);
+int b200_mc_unbind(uint64_t mc, size_t bytes);
+/* Self-tests of the runtime.  pingpong: two ranks bounce a value between one uint64 flag on
+ * each side (`peer_flag` is the other rank's flag through a peer mapping); out2_u64[0] = ns
+ * for `iters` round trips, [1] = 1 on timeout; relaxed = 0 uses st.release.sys/ld.acquire.sys,
+ * 1 the relaxed forms.  multimem: mode 0 multimem.red adds
+ * value*(i+1) into every copy of element i, mode 1 multimem.ld_reduce writes the sum of all
+ * copies to out[i], mode 2 multimem.st stores value+i into every copy. */
+int b200_selftest_pingpong(void* my_flag, void* peer_flag, int initiator, int iters, uint64_t base,
+                           int relaxed, void* out2_u64, b200_stream_t s);
+int b200_selftest_multimem(void* mc_ptr, void* out, size_t n, int mode, uint64_t value,
+                           b200_stream_t s);
 /* Stream-ordered barrier over peer memory: signal every rank, wait for every rank.
  * ws_ptrs: device array [world] of the ranks' workspace addresses; epoch grows by
  * one per call, identically on all ranks. */

@@ -72,3 +72,46 @@ def test_halo_handoff_two_gloo_ranks(built, tmp_path):
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=300,
                        env={**os.environ, "CUDA_VISIBLE_DEVICES": ""})
     assert r.returncode == 0 and "GLOO_OK" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
+
+
+FD_WORKER = textwrap.dedent('''
+    import os, sys, tempfile, torch, torch.distributed as dist
+    sys.path.insert(0, sys.argv[1])
+    from cuda_mpi_openmp_b200.parallel import DistPeerGroup
+    from cuda_mpi_openmp_b200.parallel.vmm import exchange_fds
+    dist.init_process_group("gloo")
+    g = DistPeerGroup(device=torch.device("cpu"))
+    # every rank hands each other rank two descriptors of files that name sender and receiver
+    files, out = [], {}
+    for dest in range(g.world):
+        if dest == g.rank:
+            continue
+        fds = []
+        for k in range(2):
+            f = tempfile.TemporaryFile()
+            f.write(b"from %d to %d #%d" % (g.rank, dest, k)); f.flush(); f.seek(0)
+            files.append(f); fds.append(f.fileno())
+        out[dest] = fds
+    got = exchange_fds(g, out)
+    assert sorted(got) == [r for r in range(g.world) if r != g.rank], got
+    for sender, fds in got.items():
+        for k, fd in enumerate(fds):
+            with os.fdopen(fd, "rb") as f:
+                f.seek(0)
+                assert f.read() == b"from %d to %d #%d" % (sender, g.rank, k)
+    dist.barrier()
+    if g.rank == 0:
+        print("FD_EXCHANGE_OK")
+    dist.destroy_process_group()
+''')
+
+
+def test_fd_exchange_three_gloo_ranks(built, tmp_path):
+    """The descriptor hand-off under the VMM/multicast allocator (parallel/vmm.py)."""
+    script = tmp_path / "fd_worker.py"
+    script.write_text(FD_WORKER)
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=3",
+           "--master-addr", "127.0.0.1", "--master-port", "29543", str(script), str(built)]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=300,
+                       env={**os.environ, "CUDA_VISIBLE_DEVICES": ""})
+    assert r.returncode == 0 and "FD_EXCHANGE_OK" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
