@@ -162,6 +162,68 @@ __global__ void __launch_bounds__(kClsThreads)
   }
 }
 
+// ---- two-level apply --------------------------------------------------------------
+// A random gather into the 16 MiB table costs one L2 sector per pixel, and that sector
+// rate — not HBM — bounds the plain apply kernel (profiles/ncu_prof_lab3_lut.md).  Class
+// regions are solid bodies in colour space, so most 4x4x8 cells of colours (R>>2, G>>2,
+// B>>3) map to ONE class: a 2^17-entry table of those cells fits in shared memory
+// (128 KB), and only pixels whose cell straddles a class boundary (entry kMixed) still
+// go to the full table.  Decisions stay bit-identical: a cell is marked uniform only
+// when all of its 128 full-table entries agree.
+constexpr int kCoarseBits = 17;
+constexpr size_t kCoarseBytes = size_t(1) << kCoarseBits;
+constexpr uint32_t kMixed = 0xffu;  // never a class index (classes <= 32)
+constexpr int kApplyThreads = 1024;
+
+__device__ __forceinline__ uint32_t coarse_index(uint32_t v) {
+  return ((v >> 2) & 0x3fu) | ((v >> 4) & 0xfc0u) | ((v >> 7) & 0x1f000u);
+}
+
+// thread t owns cell (rc, gc, bc) = (t & 63, (t >> 6) & 63, t >> 12): 8 x 4 words of 4 R values
+__global__ void __launch_bounds__(256)
+    lab3_lut_coarsen_kernel(const uint32_t* __restrict__ lut32, uint8_t* __restrict__ coarse) {
+  const uint32_t t = blockIdx.x * 256 + threadIdx.x;
+  const uint32_t rc = t & 63u, g0 = ((t >> 6) & 63u) * 4u, b0 = (t >> 12) * 8u;
+  const uint32_t first = lut32[(b0 << 14) | (g0 << 6) | rc] & 0xffu;
+  const uint32_t want = first * 0x01010101u;
+  bool same = true;
+#pragma unroll
+  for (uint32_t b = 0; b < 8; ++b)
+#pragma unroll
+    for (uint32_t g = 0; g < 4; ++g) same &= lut32[((b0 + b) << 14) | ((g0 + g) << 6) | rc] == want;
+  coarse[t] = (uint8_t)(same ? first : kMixed);
+}
+
+template <int U>
+__global__ void __launch_bounds__(kApplyThreads, 1)
+    lab3_lut_apply_coarse_kernel(uint32_t* __restrict__ img, int64_t n_vec,
+                                 const uint8_t* __restrict__ lut,
+                                 const uint8_t* __restrict__ coarse) {
+  extern __shared__ __align__(16) uint8_t sc[];
+  for (int i = threadIdx.x; i < (int)(kCoarseBytes / 16); i += kApplyThreads)
+    reinterpret_cast<uint4*>(sc)[i] = __ldg(reinterpret_cast<const uint4*>(coarse) + i);
+  __syncthreads();
+  auto with_class = [&](uint32_t v) {
+    uint32_t c = sc[coarse_index(v)];
+    if (c == kMixed) c = lut_gather(lut + (v & 0xffffffu));
+    return (v & 0xffffffu) | (c << 24);
+  };
+  auto apply4 = [&](uint4 v) {
+    v.x = with_class(v.x), v.y = with_class(v.y), v.z = with_class(v.z), v.w = with_class(v.w);
+    return v;
+  };
+  const int64_t stride = (int64_t)gridDim.x * kApplyThreads;
+  int64_t i = (int64_t)blockIdx.x * kApplyThreads + threadIdx.x;
+  for (; i + (U - 1) * stride < n_vec; i += U * stride) {
+    uint4 v[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) v[u] = ld_stream_u4(img + 4 * (i + u * stride));
+#pragma unroll
+    for (int u = 0; u < U; ++u) st_stream_u4(img + 4 * (i + u * stride), apply4(v[u]));
+  }
+  for (; i < n_vec; i += stride) st_stream_u4(img + 4 * i, apply4(ld_stream_u4(img + 4 * i)));
+}
+
 __global__ void lab3_lut_apply_scalar_kernel(uint32_t* __restrict__ img, int64_t begin, int64_t n,
                                              const uint8_t* __restrict__ lut) {
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
@@ -173,6 +235,54 @@ __global__ void lab3_lut_apply_scalar_kernel(uint32_t* __restrict__ img, int64_t
 
 constexpr size_t kLutBytes = size_t(1) << 24;
 constexpr int64_t kLutMinPixels = int64_t(1) << 25;
+
+// Image pass against a complete table.  `coarse` (kCoarseBytes, may be null) is filled
+// here and enables the two-level kernel; B200LABS_LAB3_COARSE=0 forces the plain one.
+static int run_lut_apply(uint32_t* img, int64_t npix, const uint8_t* lut, uint8_t* coarse,
+                         cudaStream_t st) {
+  const int sms = device_info().sm_count;
+  const bool aligned = (((uintptr_t)img) & 15u) == 0;
+  const int64_t n_vec = aligned ? npix / 4 : 0;
+  const int64_t tail = n_vec * 4;
+  auto grid_for = [&](int64_t items, int threads, int per_sm) {
+    int64_t want = (items + threads - 1) / threads;
+    int64_t cap = (int64_t)sms * per_sm;
+    return (int)(want < cap ? (want > 0 ? want : 1) : cap);
+  };
+  static const bool coarse_off = [] {
+    const char* e = getenv("B200LABS_LAB3_COARSE");
+    return e && !strcmp(e, "0");
+  }();
+  // below ~2^22 pixels loading 128 KB per SM costs more than the gathers it saves
+  const bool two_level = coarse && !coarse_off && (((uintptr_t)coarse) & 15u) == 0 &&
+                         n_vec >= (int64_t(1) << 20);
+  if (n_vec && two_level) {
+    static bool attr_set[64] = {false};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (!attr_set[dev & 63]) {
+      B200_CUDA_OK(cudaFuncSetAttribute(lab3_lut_apply_coarse_kernel<4>,
+                                        cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        (int)kCoarseBytes));
+      attr_set[dev & 63] = true;
+    }
+    lab3_lut_coarsen_kernel<<<(unsigned)(kCoarseBytes / 256), 256, 0, st>>>((const uint32_t*)lut,
+                                                                           coarse);
+    B200_LAUNCH_OK();
+    lab3_lut_apply_coarse_kernel<4><<<grid_for(n_vec, kApplyThreads, 1), kApplyThreads,
+                                      kCoarseBytes, st>>>(img, n_vec, lut, coarse);
+    B200_LAUNCH_OK();
+  } else if (n_vec) {
+    lab3_lut_apply_kernel<<<grid_for(n_vec, kClsThreads, 8), kClsThreads, 0, st>>>(img, n_vec, lut);
+    B200_LAUNCH_OK();
+  }
+  if (tail < npix) {
+    lab3_lut_apply_scalar_kernel<<<grid_for(npix - tail, kClsThreads, 8), kClsThreads, 0, st>>>(
+        img, tail, npix, lut);
+    B200_LAUNCH_OK();
+  }
+  return 0;
+}
 
 static int pick_variant(int64_t npix, int variant, size_t scratch_bytes) {
   if (variant != B200_CLASSIFY_AUTO) return variant;
@@ -207,8 +317,10 @@ extern "C" int b200_lab3_finalize(const long long* moments, int nc, double* para
 }
 
 extern "C" size_t b200_lab3_classify_scratch_bytes(int64_t npix, int variant) {
-  if (variant == B200_CLASSIFY_LUT) return kLutBytes;
-  if (variant == B200_CLASSIFY_AUTO && npix >= kLutMinPixels) return kLutBytes;
+  // full table + the coarse table of the two-level apply (kLutBytes alone still works:
+  // the image pass then uses the one-level kernel)
+  if (variant == B200_CLASSIFY_LUT) return kLutBytes + kCoarseBytes;
+  if (variant == B200_CLASSIFY_AUTO && npix >= kLutMinPixels) return kLutBytes + kCoarseBytes;
   return 0;
 }
 
@@ -253,17 +365,8 @@ extern "C" int b200_lab3_classify(void* img, int64_t npix, int nc, const double*
           (uint8_t*)scratch, nc, params);
     }
     B200_LAUNCH_OK();
-    if (n_vec) {
-      lab3_lut_apply_kernel<<<grid_for(n_vec, 8), kClsThreads, 0, st>>>((uint32_t*)img, n_vec,
-                                                                        (const uint8_t*)scratch);
-      B200_LAUNCH_OK();
-    }
-    if (tail < npix) {
-      lab3_lut_apply_scalar_kernel<<<grid_for(npix - tail, 8), kClsThreads, 0, st>>>(
-          (uint32_t*)img, tail, npix, (const uint8_t*)scratch);
-      B200_LAUNCH_OK();
-    }
-    return 0;
+    uint8_t* coarse = scratch_bytes >= kLutBytes + kCoarseBytes ? (uint8_t*)scratch + kLutBytes : nullptr;
+    return run_lut_apply((uint32_t*)img, npix, (const uint8_t*)scratch, coarse, st);
   }
   B200_REQUIRE(variant == B200_CLASSIFY_DIRECT, "lab3: unknown classify variant %d", variant);
   if (n_vec) {
@@ -292,27 +395,11 @@ extern "C" int b200_lab3_classify_geom(void* img, int64_t npix, int nc, const do
 
 // Image pass only, against a colour table that is already complete (built by
 // b200_lab3_classify's LUT variant or cooperatively by b200_lab3_lut_build_allgather).
-extern "C" int b200_lab3_apply_lut(void* img, int64_t npix, const void* lut, b200_stream_t s) {
+extern "C" int b200_lab3_apply_lut(void* img, int64_t npix, const void* lut, void* coarse_scratch,
+                                   b200_stream_t s) {
   if (npix <= 0) return 0;
-  cudaStream_t st = as_stream(s);
-  const int sms = device_info().sm_count;
-  const bool aligned = (((uintptr_t)img) & 15u) == 0;
-  const int64_t n_vec = aligned ? npix / 4 : 0;
-  const int64_t tail = n_vec * 4;
-  auto grid_for = [&](int64_t items) {
-    int64_t want = (items + kClsThreads - 1) / kClsThreads;
-    int64_t cap = (int64_t)sms * 8;
-    return (int)(want < cap ? (want > 0 ? want : 1) : cap);
-  };
-  if (n_vec) {
-    lab3_lut_apply_kernel<<<grid_for(n_vec), kClsThreads, 0, st>>>((uint32_t*)img, n_vec,
-                                                                   (const uint8_t*)lut);
-    B200_LAUNCH_OK();
-  }
-  if (tail < npix) {
-    lab3_lut_apply_scalar_kernel<<<grid_for(npix - tail), kClsThreads, 0, st>>>(
-        (uint32_t*)img, tail, npix, (const uint8_t*)lut);
-    B200_LAUNCH_OK();
-  }
-  return 0;
+  return run_lut_apply((uint32_t*)img, npix, (const uint8_t*)lut, (uint8_t*)coarse_scratch,
+                       as_stream(s));
 }
+
+extern "C" size_t b200_lab3_coarse_bytes(void) { return kCoarseBytes; }

@@ -242,29 +242,48 @@ __global__ void __launch_bounds__(kCountThreads)
 }
 
 // ---------------------------------------------------------- fused partition+exchange
-constexpr int kPartThreads = 512;
+constexpr int kPartThreads = 256;  // 4 CTAs per SM
 constexpr int kPartWarps = kPartThreads / 32;
 constexpr int kPartItems = 16;
-constexpr int kPartTile = kPartThreads * kPartItems;  // 8192 keys
+constexpr int kPartTile = kPartThreads * kPartItems;  // 4096 keys
+constexpr int kDestLutBits = 12;
+constexpr uint32_t kDestAmbiguous = 0x80u, kNoDest = 8u;
 
 struct PartTargets {
   uint32_t* bucket[kMaxWorld];              // destination buckets (peer-mapped or local)
   unsigned long long* cursor[kMaxWorld];    // their fill cursors (remote atomics)
 };
 
+// One tile = 4096 keys, 16 per thread.  The kernel was ALU-bound when it ranked keys with
+// ballots (111 Gkeys/s, profiles/ncu_prof_mgpu.md), so the per-key work is now mostly
+// table look-ups:
+//  * destination: the key range spanned by the splitters is cut into 4096 equal buckets; a
+//    shared-memory table gives the destination of a bucket, or "ambiguous" when a splitter
+//    key lies inside it — only those keys run the exact comparison against the 64-bit
+//    composites;
+//  * slot: the partition need not be stable (the bucket is sorted afterwards), so a thread
+//    counts its own keys per destination in packed 8-bit register counters, a warp scan of
+//    those counters plus a scan over the warps gives the thread's first slot per
+//    destination, and a key's slot is that plus its rank among the thread's own keys
+//    (private shared-memory counters instead of registers were measured slower: LSU-bound);
+//  * the destination byte is staged beside the key, so the output loop does not search.
 template <int KT>
-__global__ void __launch_bounds__(kPartThreads, 2)
+__global__ void __launch_bounds__(kPartThreads, 1024 / kPartThreads)
     sort_partition_scatter_kernel(const uint32_t* __restrict__ keys, unsigned long long n_local,
                                   const unsigned long long* __restrict__ splitters, int idx_bits,
                                   PartTargets tg, unsigned long long capacity, SymmPeers peers,
                                   int rank, int world, uint64_t epoch, int phase_mask,
                                   unsigned long long timeout_ns) {
   __shared__ uint32_t s_keys[kPartTile];
-  __shared__ uint32_t warp_cnt[kPartWarps][kMaxWorld];
-  __shared__ uint32_t tile_start[kMaxWorld + 1];
-  __shared__ unsigned long long base[kMaxWorld];
+  __shared__ uint8_t s_dst[kPartTile];
+  __shared__ uint8_t dest_lut[1 << kDestLutBits];
+  // per-warp totals and run starts, two 16-bit fields per word: (d0,d1) (d2,d3) (d4,d5) (d6,d7)
+  __shared__ __align__(16) uint32_t warp_tot[kPartWarps][kMaxWorld / 2];
+  __shared__ __align__(16) uint16_t warp_off[kPartWarps][kMaxWorld];
+  __shared__ uint32_t tile_total[kMaxWorld];
+  __shared__ uint32_t* s_bias[kMaxWorld + 1];  // bucket + reserved base - tile start; null = dropped
   __shared__ uint32_t s_hi[kMaxWorld], s_lo[kMaxWorld];
-  __shared__ uint32_t* s_bucket[kMaxWorld];          // dynamically indexed: keep out of
+  __shared__ uint32_t* s_bucket[kMaxWorld];            // dynamically indexed: keep out of
   __shared__ unsigned long long* s_cursor[kMaxWorld];  // param space (no local-memory copy)
   __shared__ bool is_last;
   SymmWorkspace* me = peers.ws[rank];
@@ -282,91 +301,157 @@ __global__ void __launch_bounds__(kPartThreads, 2)
         s_bucket[k] = tg.bucket[k];
         s_cursor[k] = tg.cursor[k];
       }
+    if (tid == 0) s_bias[kMaxWorld] = nullptr;
+    __syncthreads();
+    // ---- destination table over [first splitter key, last splitter key]
+    const uint32_t lut_base = world > 1 ? s_hi[1] : 0xffffffffu;
+    const uint32_t lut_span = world > 1 ? s_hi[world - 1] - lut_base : 0u;
+    const int lut_shift = lut_span < (1u << kDestLutBits) ? 0 : 32 - kDestLutBits - __clz(lut_span);
+    for (int bkt = tid; bkt < (1 << kDestLutBits); bkt += kPartThreads) {
+      const unsigned long long lo = (unsigned long long)lut_base + ((unsigned long long)bkt << lut_shift);
+      const unsigned long long hi = lo + ((1ull << lut_shift) - 1);
+      uint32_t below = 0, upto = 0;
+#pragma unroll
+      for (int k = 1; k < kMaxWorld; ++k)
+        if (k < world) {
+          below += (unsigned long long)s_hi[k] < lo ? 1u : 0u;
+          upto += (unsigned long long)s_hi[k] <= hi ? 1u : 0u;
+        }
+      dest_lut[bkt] = (uint8_t)(below | (upto != below ? kDestAmbiguous : 0u));
+    }
+    __syncthreads();
     const uint32_t src_bits = idx_bits >= 32 ? 0u : ((uint32_t)rank << idx_bits);
     const unsigned long long n_tiles = (n_local + kPartTile - 1) / kPartTile;
     // persistent: a CTA walks tiles blockIdx.x, +gridDim.x, ... and fences its remote
     // stores ONCE at the end (a system-scope fence per tile cost ~10 us of NVLink
     // round trip per tile and made this kernel 3x slower)
     for (unsigned long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-      for (int i = tid; i < kPartWarps * kMaxWorld; i += kPartThreads) (&warp_cnt[0][0])[i] = 0;
-      __syncthreads();  // also: previous tile's s_keys / tile_start / base fully consumed
       const unsigned long long tile_base = tile * kPartTile;
       const uint32_t n_valid = (uint32_t)min((unsigned long long)kPartTile, n_local - tile_base);
 
       uint32_t key[kPartItems];
-      uint32_t dr[kPartItems];  // destination << 16 | rank inside (warp, destination)
       const uint32_t w_off = warp * (kPartItems * 32) + lane;
-      const uint32_t le_mask = 0xffffffffu >> (31 - lane);
 #pragma unroll
       for (int i = 0; i < kPartItems; ++i) {
         const uint32_t o = w_off + i * 32;
         key[i] = o < n_valid ? ld_stream_u32(keys + tile_base + o) : 0u;
       }
+      // ---- destinations from the table; meta byte per key: destination (8 = none)
+      uint32_t meta[kPartItems / 4] = {};
 #pragma unroll
       for (int i = 0; i < kPartItems; ++i) {
         const uint32_t o = w_off + i * 32;
-        const bool valid = o < n_valid;
-        int d = dest_of(to_ordered_mg<KT>(key[i]), src_bits | (uint32_t)(tile_base + o), s_hi, s_lo, world);
-        if (!valid) d = kMaxWorld;  // padding: no destination
-        const uint32_t peers_mask = match_any_bits<4>((uint32_t)d);  // d <= kMaxWorld = 8
-        const int leader = 31 - __clz(peers_mask);
-        const uint32_t below_incl = __popc(peers_mask & le_mask);
-        uint32_t old = 0;
-        if (valid && lane == leader) {
-          old = warp_cnt[warp][d];
-          warp_cnt[warp][d] = old + below_incl;
+        const uint32_t x = to_ordered_mg<KT>(key[i]);
+        const uint32_t t = (x - lut_base) >> lut_shift;
+        uint32_t e = dest_lut[t < (1u << kDestLutBits) ? t : 0u];
+        e = t < (1u << kDestLutBits) ? e : (uint32_t)(world - 1);  // above every splitter
+        e = x < lut_base ? 0u : e;                                  // below every splitter
+        if (e & kDestAmbiguous) {
+          // a splitter key lies in this key's table bucket (a fraction of a percent of random
+          // keys): count the splitters whose 64-bit composite is <= mine
+          const uint32_t low = src_bits | (uint32_t)(tile_base + o);
+          e = 0;
+#pragma unroll
+          for (int k = 1; k < kMaxWorld; ++k)
+            if (k < world) e += (s_hi[k] < x || (s_hi[k] == x && s_lo[k] <= low)) ? 1u : 0u;
         }
-        old = __shfl_sync(0xffffffffu, old, leader);
-        dr[i] = ((uint32_t)d << 16) | (old + below_incl - 1);
-        __syncwarp();
+        e = o < n_valid ? e : kNoDest;
+        meta[i >> 2] |= e << (8 * (i & 3));
       }
-      __syncthreads();
-      // per destination: offsets of the warps, tile total, reservation
-      if (tid < world) {
-        uint32_t run = 0;
-        for (int wv = 0; wv < kPartWarps; ++wv) {
-          const uint32_t c = warp_cnt[wv][tid];
-          warp_cnt[wv][tid] = run;
-          run += c;
-        }
-        tile_start[tid + 1] = run;  // totals for now, scanned below
-        unsigned long long b = 0;
-        if (phase_mask & 8) {
-          // my segment in that rank's bucket was reserved by sort_count_reserve_kernel:
-          // sub-allocate it with a LOCAL atomic (no NVLink round trip on the tile's path)
-          if (run) b = atomicAdd(&me->sort_local_cursor[tid], (unsigned long long)run);
-          if (b + run > capacity) b = ~0ull;  // reservation failed earlier (error word is set)
-        } else {
-          if (run) b = atomicAdd_system(s_cursor[tid], (unsigned long long)run);
-          if (b + run > capacity) {
-            atomicOr(&me->error, (unsigned long long)kErrSortOverflow);
-            b = ~0ull;  // poison: this tile's keys for that destination are dropped
-          }
-        }
-        base[tid] = b;
-      }
-      __syncthreads();
-      if (tid == 0) {
-        tile_start[0] = 0;
-        for (int d = 0; d < world; ++d) tile_start[d + 1] += tile_start[d];
-      }
-      __syncthreads();
+      // ---- count per destination in packed 8-bit registers (destinations 0-3 / 4-7);
+      // rank among my own keys -> meta bits 4-7
+      uint32_t c_lo = 0, c_hi = 0;
 #pragma unroll
       for (int i = 0; i < kPartItems; ++i) {
-        const int d = (int)(dr[i] >> 16);
-        if (d < kMaxWorld) s_keys[tile_start[d] + warp_cnt[warp][d] + (dr[i] & 0xffffu)] = key[i];
+        const uint32_t d = (meta[i >> 2] >> (8 * (i & 3))) & 0xfu;
+        const uint32_t sh = (d & 3u) << 3;
+        const bool hi = (d & 4u) != 0;
+        const uint32_t r = ((hi ? c_hi : c_lo) >> sh) & 0xffu;
+        const uint32_t inc = d < kNoDest ? (1u << sh) : 0u;
+        c_lo += hi ? 0u : inc;
+        c_hi += hi ? inc : 0u;
+        meta[i >> 2] |= (d < kNoDest ? r : 0u) << (8 * (i & 3) + 4);
+      }
+      // ---- warp scan of the counters, widened to 16 bits
+      const uint2 c = make_uint2(c_lo, c_hi);
+      uint32_t f[4] = {__byte_perm(c.x, 0, 0x4140), __byte_perm(c.x, 0, 0x4342),
+                       __byte_perm(c.y, 0, 0x4140), __byte_perm(c.y, 0, 0x4342)};
+      uint32_t excl[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) excl[k] = f[k];
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const uint32_t t = __shfl_up_sync(0xffffffffu, f[k], o);
+          if (lane >= o) f[k] += t;
+        }
+      }
+#pragma unroll
+      for (int k = 0; k < 4; ++k) excl[k] = f[k] - excl[k];
+      __syncthreads();  // previous tile's s_keys / s_dst / warp_off / s_bias fully consumed
+      if (lane == 31) *reinterpret_cast<uint4*>(warp_tot[warp]) = make_uint4(f[0], f[1], f[2], f[3]);
+      __syncthreads();
+      // ---- per destination: runs of the warps, tile total, reservation in the bucket
+      unsigned long long b = 0;
+      uint32_t run = 0;
+      if (tid < kMaxWorld) {
+        const int word = tid >> 1, shf = (tid & 1) * 16;
+#pragma unroll
+        for (int wv = 0; wv < kPartWarps; ++wv) {
+          warp_off[wv][tid] = (uint16_t)run;
+          run += (warp_tot[wv][word] >> shf) & 0xffffu;
+        }
+        tile_total[tid] = run;
+        if (tid < world) {
+          if (phase_mask & 8) {
+            // my segment in that rank's bucket was reserved by sort_count_reserve_kernel:
+            // sub-allocate it with a LOCAL atomic (no NVLink round trip on the tile's path)
+            if (run) b = atomicAdd(&me->sort_local_cursor[tid], (unsigned long long)run);
+            if (b + run > capacity) b = ~0ull;  // reservation failed earlier (error word is set)
+          } else {
+            if (run) b = atomicAdd_system(s_cursor[tid], (unsigned long long)run);
+            if (b + run > capacity) {
+              atomicOr(&me->error, (unsigned long long)kErrSortOverflow);
+              b = ~0ull;  // poison: this tile's keys for that destination are dropped
+            }
+          }
+        }
       }
       __syncthreads();
-      // runs of equal destination leave as contiguous (mostly remote) stores
+      if (tid < kMaxWorld) {
+        uint32_t start = 0;
+#pragma unroll
+        for (int k = 0; k < kMaxWorld; ++k) start += k < tid ? tile_total[k] : 0u;
+#pragma unroll
+        for (int wv = 0; wv < kPartWarps; ++wv) warp_off[wv][tid] = (uint16_t)(warp_off[wv][tid] + start);
+        s_bias[tid] = (tid < world && b != ~0ull) ? s_bucket[tid] + b - start : nullptr;
+      }
+      __syncthreads();
+      // ---- stage keys (and their destination bytes) in destination order
+      {
+        const uint4 wo = *reinterpret_cast<const uint4*>(warp_off[warp]);
+        const uint32_t g0 = wo.x + excl[0], g1 = wo.y + excl[1], g2 = wo.z + excl[2], g3 = wo.w + excl[3];
+#pragma unroll
+        for (int i = 0; i < kPartItems; ++i) {
+          const uint32_t m = (meta[i >> 2] >> (8 * (i & 3))) & 0xffu;
+          const uint32_t d = m & 0xfu;
+          if (d < kNoDest) {
+            const uint32_t g = (d & 4u) ? ((d & 2u) ? g3 : g2) : ((d & 2u) ? g1 : g0);
+            const uint32_t pos = ((g >> ((d & 1u) << 4)) & 0xffffu) + (m >> 4);
+            s_keys[pos] = key[i];
+            s_dst[pos] = (uint8_t)d;
+          }
+        }
+      }
+      __syncthreads();
+      // ---- runs of equal destination leave as contiguous (mostly remote) stores
 #pragma unroll
       for (int i = 0; i < kPartItems; ++i) {
         const uint32_t p = tid + i * kPartThreads;
         if (p < n_valid) {
-          int d = 0;
-#pragma unroll
-          for (int k = 1; k < kMaxWorld; ++k) d += (k < world && tile_start[k] <= p) ? 1 : 0;
-          const unsigned long long b = base[d];
-          if (b != ~0ull) s_bucket[d][b + (p - tile_start[d])] = s_keys[p];
+          uint32_t* dst = s_bias[s_dst[p]];
+          if (dst) dst[p] = s_keys[p];
         }
       }
     }
@@ -470,7 +555,7 @@ extern "C" int b200_sort_mgpu_scatter(const void* keys, size_t n_local, int key_
   unsigned grid = 1u;
   if (phase_mask & 1) {
     const size_t tiles = (n_local + kPartTile - 1) / kPartTile;
-    const size_t resident = (size_t)device_info().sm_count * 2;  // 2 CTAs of 512 threads per SM
+    const size_t resident = (size_t)device_info().sm_count * (1024 / kPartThreads);
     grid = (unsigned)(tiles < resident ? tiles : resident);
   }
   cudaStream_t st = as_stream(s);

@@ -35,7 +35,8 @@ N.register("b200_lab3_stats_nvls", C.c_int,
 N.register("b200_lab3_lut_build_allgather", C.c_int,
            [C.POINTER(C.c_void_p), C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_uint64, C.c_int,
             C.c_void_p])
-N.register("b200_lab3_apply_lut", C.c_int, [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p])
+N.register("b200_lab3_apply_lut", C.c_int, [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p])
+N.register("b200_lab3_coarse_bytes", C.c_size_t, [])
 N.register("b200_sort_mgpu_splitters", C.c_int,
            [C.c_void_p, C.c_size_t, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_uint64, C.c_int,
             C.c_void_p])
@@ -150,9 +151,11 @@ def lut_build_allgather(lut_ptrs: Sequence[int], nc: int, params: torch.Tensor, 
             "b200_lab3_lut_build_allgather")
 
 
-def apply_lut(img: torch.Tensor, lut_addr: int) -> torch.Tensor:
+def apply_lut(img: torch.Tensor, lut_addr: int, coarse: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Image pass against a finished colour table; ``coarse`` (uint8[b200_lab3_coarse_bytes()])
+    turns on the two-level lookup (cell table in shared memory, see csrc/lab3_classify.cu)."""
     N.check(N.lib().b200_lab3_apply_lut(N.ptr(img), img.shape[0] * img.shape[1], C.c_void_p(lut_addr),
-                                        N.current_stream_ptr()), "b200_lab3_apply_lut")
+                                        N.ptr(coarse), N.current_stream_ptr()), "b200_lab3_apply_lut")
     return img
 
 
@@ -198,8 +201,11 @@ class ShardedClassifier:
         lut = need > 0
         self.coop_lut = lut and impl == "fused" and group.world > 1 and group.world & (group.world - 1) == 0
         self.sym_lut = group.alloc(1 << 24) if self.coop_lut else None
-        # kernels per step: stats(1) [+ finalize for nccl] + classify (lut: build + apply)
-        self.launches_per_step = (1 if impl == "fused" else 2) + (2 if lut else 1)
+        self.coarse = (torch.empty(int(N.lib().b200_lab3_coarse_bytes()), dtype=torch.uint8, device=dev)
+                       if self.coop_lut else None)
+        # kernels per step: stats(1) [+ finalize for nccl] + classify (lut: build + cell table + apply)
+        two_level = lut and npix >= (1 << 22)
+        self.launches_per_step = (1 if impl == "fused" else 2) + ((3 if two_level else 2) if lut else 1)
 
     def fit(self) -> torch.Tensor:
         g = self.group
@@ -226,7 +232,7 @@ class ShardedClassifier:
             g = self.group
             lut_build_allgather(self.sym_lut.peer_ptrs, self.nc, self.params, self.ws.ptrs_dev, g.rank,
                                 g.world, g.next_epoch(), 3)
-            return apply_lut(self.band, self.sym_lut.local_ptr)
+            return apply_lut(self.band, self.sym_lut.local_ptr, self.coarse)
         return CL.lab3_classify(self.band, self.params, variant=self.variant, scratch=self.scratch)
 
     def free(self) -> None:

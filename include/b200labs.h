@@ -214,7 +214,13 @@ int b200_lab3_stats_nvls(const void* img, int w, int64_t y0, int64_t h_local, co
 int b200_lab3_lut_build_allgather(void* const* lut_ptrs, int nc, const double* params,
                                   const void* ws_ptrs, int rank, int world, uint64_t epoch,
                                   int phase_mask, b200_stream_t s);
-int b200_lab3_apply_lut(void* img, int64_t npix, const void* lut, b200_stream_t s);
+/* coarse_scratch: b200_lab3_coarse_bytes() bytes (16-byte aligned) or NULL.  When given
+ * (and the image has >= 2^22 pixels) a 2^17-entry table of 4x4x8 colour cells is derived
+ * from `lut`, kept in shared memory, and only pixels in cells that straddle a class
+ * boundary still gather from the 16 MiB table.  Same output either way. */
+int b200_lab3_apply_lut(void* img, int64_t npix, const void* lut, void* coarse_scratch,
+                        b200_stream_t s);
+size_t b200_lab3_coarse_bytes(void);
 
 /* lab5 fused sample sort, step 1: sample + exchange + splitters (one CTA). */
 int b200_sort_mgpu_splitters(const void* keys, size_t n_local, int key_type,

@@ -172,6 +172,54 @@ def test_lab3_classify_bit_exact(cuda_device, variant):
     assert torch.equal(got[clear], dist.argmin(dim=0)[clear]) and clear.float().mean() > 0.99
 
 
+@pytest.mark.parametrize("kind", ["noise", "separated"])
+def test_lab3_two_level_apply_matches_one_level(cuda_device, kind):
+    """>= 2^22 pixels + full scratch -> the image pass looks colours up in a shared-memory table
+    of 4x4x8 colour cells first and in the 16 MiB table only for cells that straddle a class
+    boundary.  Must equal the one-level pass (16 MiB scratch only) and the direct fp64 kernel."""
+    rng = np.random.default_rng(23)
+    h, w = 2048, 2304 + 1                               # 4.7 M pixels, odd count -> scalar tail too
+    img = rng.integers(0, 256, size=(h, w, 4), dtype=np.uint8)
+    if kind == "noise":                                 # near-identical classes: ragged boundaries
+        classes = random_classes(rng, w, h, 32, 300)
+    else:                                               # 4 colour blobs sampled from 4 image quadrants
+        centres = np.array([[40, 50, 60], [200, 60, 70], [60, 210, 90], [120, 130, 220]])
+        for q, (ys, xs) in enumerate([(slice(0, 1024), slice(0, 1152)), (slice(0, 1024), slice(1152, w)),
+                                      (slice(1024, h), slice(0, 1152)), (slice(1024, h), slice(1152, w))]):
+            blk = img[ys, xs, :3]
+            blk[...] = np.clip(centres[q] + rng.normal(0, 12, blk.shape), 0, 255).astype(np.uint8)
+        boxes = [(0, 1024, 0, 1152), (0, 1024, 1152, w), (1024, h, 0, 1152), (1024, h, 1152, w)]
+        classes = [np.stack([rng.integers(x0, x1, 400), rng.integers(y0, y1, 400)], axis=1) for y0, y1, x0, x1 in boxes]
+        img[::7, ::5, :3] = rng.integers(0, 256, size=img[::7, ::5, :3].shape, dtype=np.uint8)   # every cell gets visitors
+    d0 = torch.from_numpy(img).to(cuda_device)
+    params = ops.lab3_params_from_points(d0, classes)
+    full = int(N.lib().b200_lab3_classify_scratch_bytes(h * w, ops.classify.CLASSIFY_VARIANTS["lut"]))
+    coarse_bytes = int(N.lib().b200_lab3_coarse_bytes())
+    assert full == (1 << 24) + coarse_bytes
+    outs = {}
+    for name, variant, nbytes in (("two_level", "lut", full), ("one_level", "lut", 1 << 24), ("direct", "direct", 0)):
+        d = d0.clone()
+        scratch = torch.full((max(nbytes, 1),), 0xEE, dtype=torch.uint8, device=cuda_device)
+        N.check(N.lib().b200_lab3_classify(N.ptr(d), h * w, len(classes), N.ptr(params),
+                                           ops.classify.CLASSIFY_VARIANTS[variant], N.ptr(scratch) if nbytes else None,
+                                           nbytes, N.current_stream_ptr()), "classify")
+        outs[name] = d.cpu().numpy()
+        if name == "two_level":
+            lut = scratch[: 1 << 24].cpu().numpy()
+            cells = scratch[1 << 24:].cpu().numpy()
+    assert np.array_equal(outs["two_level"], outs["one_level"])
+    assert np.array_equal(outs["two_level"], outs["direct"])
+    # the cell table: uniform cells name the class of all their 128 colours, the rest say "mixed"
+    mixed = cells == 0xFF
+    assert 0 < mixed.sum() < cells.size, "expected both uniform and mixed cells"
+    cube = lut.reshape(32, 8, 64, 4, 64, 4)            # B = (bc, b), G = (gc, g), R = (rc, r)
+    lo, hi = cube.min(axis=(1, 3, 5)), cube.max(axis=(1, 3, 5))
+    want_cells = np.where(lo == hi, lo, 0xFF).astype(np.uint8).reshape(-1)   # index = bc<<12 | gc<<6 | rc
+    assert np.array_equal(cells, want_cells)
+    if kind == "separated":
+        assert mixed.mean() < 0.25
+
+
 def test_lab3_geom_and_golden(cuda_device, repo_root, tmp_path):
     src = ImgData(str(repo_root / "lab3/data/test_01_lab3.txt"), out_dir=str(tmp_path), materialize=False).rgba
     gold = ImgData(str(repo_root / "lab3/data_out_gt/test_01_lab3.txt"), out_dir=str(tmp_path), materialize=False).rgba
