@@ -128,6 +128,8 @@ def run_own(args):
     clock_summary = clocks.summary()
     # context: a plain device-to-device copy of the same band (same bytes read + written)
     copy_ms = timed_steps(group, lambda: model.out.copy_(model.band), 5, 2)
+    model.step()                                       # model.out holds the filter output again
+    torch.cuda.synchronize()
     total_bytes = BYTES_PER_PX * w * h
     value = total_bytes / ms / 1e6
     peak, peak_kind = peak_gbs()

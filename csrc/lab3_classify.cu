@@ -129,7 +129,7 @@ __global__ void __launch_bounds__(kLutThreads)
     lab3_lut_build_hoisted_kernel(uint8_t* __restrict__ lut, int nc, const double* __restrict__ params) {
   extern __shared__ __align__(16) uint8_t lut_smem_raw[];
   LutSmem& S = *reinterpret_cast<LutSmem*>(lut_smem_raw);
-  const int g = blockIdx.x >> 2, r0 = (blockIdx.x & 3) * kLutR;
+  const int g = blockIdx.x / (256 / kLutR), r0 = (blockIdx.x % (256 / kLutR)) * kLutR;
   lut_build_block(S, nc, params, g, r0, 0, 256, [&](uint32_t id, uint8_t cls) { lut[id] = cls; });
 }
 

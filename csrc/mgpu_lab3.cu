@@ -168,7 +168,7 @@ __global__ void __launch_bounds__(kLutThreads)
   if (phase_mask & 1) {
     if (tid < kMaxWorld) s_lut[tid] = tid < world ? tg.lut[(rank + tid) % world] : nullptr;  // own copy first
     const int per_rank = 256 / world;
-    const int g = blockIdx.x >> 2, r0 = (blockIdx.x & 3) * kLutR;
+    const int g = blockIdx.x / (256 / kLutR), r0 = (blockIdx.x % (256 / kLutR)) * kLutR;
     lut_build_block(S, nc, params, g, r0, rank * per_rank, (rank + 1) * per_rank,
                     [&](uint32_t id, uint8_t cls) {
                       for (int p = 0; p < world; ++p) s_lut[p][id] = cls;
