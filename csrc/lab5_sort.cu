@@ -35,6 +35,9 @@ constexpr int kTile = kSortThreads * kItems;  // 8192 keys
 #ifndef B200_SORT_PERSIST_DEFAULT
 #define B200_SORT_PERSIST_DEFAULT 0
 #endif
+#ifndef B200_SORT_LOOK
+#define B200_SORT_LOOK 8   /* 16 measured 6% slower */
+#endif
 #ifndef B200_SORT_BALLOT_ITEMS
 #define B200_SORT_BALLOT_ITEMS 0
 #endif
@@ -143,7 +146,12 @@ struct NoHook {
   __device__ __forceinline__ void operator()() const {}
 };
 
-template <int KT, int NM, bool FULL, bool PREFETCHED = false, typename Hook = NoHook>
+// UNSTABLE: a keys-only LSD sort needs stability only to keep the order made by EARLIER
+// passes, so the first pass may place equal digits in any order.  It then ranks a key with
+// one shared-memory atomicAdd on a per-tile digit counter (rank inside the tile directly)
+// instead of finding its same-digit lanes: ~6 shared-memory operations per key become one.
+template <int KT, int NM, bool FULL, bool PREFETCHED = false, typename Hook = NoHook,
+          bool UNSTABLE = false>
 __device__ __forceinline__ void sweep_tile(SweepSmem& S, const uint32_t* __restrict__ in,
                                            uint32_t* __restrict__ out, size_t tile_base,
                                            uint32_t n_valid, uint32_t tile, int pass,
@@ -173,35 +181,47 @@ __device__ __forceinline__ void sweep_tile(SweepSmem& S, const uint32_t* __restr
   uint32_t* wh = S.warp_hist[warp];
   uint32_t* lb = S.lane_bits[warp];
   const uint32_t le_mask = 0xffffffffu >> (31 - lane);
+  if (UNSTABLE) {
+    // warp_hist[0][] doubles as the per-tile digit counter (zeroed by the kernel prologue)
 #pragma unroll
-  for (int i = 0; i < kItems; ++i) {
-    // padding keys rank as digit 255 *after* every real key (they come last)
-    uint32_t d = (to_ordered<KT>(key[i]) >> shift) & 0xff;
-    if (!FULL && (w_off + i * 32) >= n_valid) d = 0xffu;
-    uint32_t peers;
-    const bool via_smem = i >= NM;  // compile-time after unrolling
-    if (via_smem) {
-      // match through shared memory: every lane ORs its bit into the word of its
-      // digit, then reads the word back — three LSU operations instead of 40 ALU ones
-      atomicOr(&lb[d], 1u << lane);
-      __syncwarp();
-      peers = lb[d];
-      __syncwarp();
-    } else {
-      peers = match_any_bits<kRadixBits>(d);
+    for (int i = 0; i < kItems; ++i) {
+      const uint32_t d = (to_ordered<KT>(key[i]) >> shift) & 0xff;
+      if (FULL || (w_off + i * 32) < n_valid)
+        dr[i] = (d << 16) | atomicAdd(&S.warp_hist[0][d], 1u);  // rank < kTile = 2^13
+      else
+        dr[i] = 0xffffffffu;  // padding: not counted, not staged
     }
-    const int leader = 31 - __clz(peers);
-    const uint32_t below_incl = __popc(peers & le_mask);  // on the leader: the group size
-    uint32_t old = 0;
-    if (lane == leader) {
-      old = wh[d];
-      wh[d] = old + below_incl;
-      if (via_smem) lb[d] = 0;  // leave the word clean for the next key
+  } else {
+#pragma unroll
+    for (int i = 0; i < kItems; ++i) {
+      // padding keys rank as digit 255 *after* every real key (they come last)
+      uint32_t d = (to_ordered<KT>(key[i]) >> shift) & 0xff;
+      if (!FULL && (w_off + i * 32) >= n_valid) d = 0xffu;
+      uint32_t peers;
+      const bool via_smem = i >= NM;  // compile-time after unrolling
+      if (via_smem) {
+        // match through shared memory: every lane ORs its bit into the word of its
+        // digit, then reads the word back — three LSU operations instead of 40 ALU ones
+        atomicOr(&lb[d], 1u << lane);
+        __syncwarp();
+        peers = lb[d];
+        __syncwarp();
+      } else {
+        peers = match_any_bits<kRadixBits>(d);
+      }
+      const int leader = 31 - __clz(peers);
+      const uint32_t below_incl = __popc(peers & le_mask);  // on the leader: the group size
+      uint32_t old = 0;
+      if (lane == leader) {
+        old = wh[d];
+        wh[d] = old + below_incl;
+        if (via_smem) lb[d] = 0;  // leave the word clean for the next key
+      }
+      old = __shfl_sync(0xffffffffu, old, leader);
+      dr[i] = (d << 16) | (old + below_incl - 1);
+      __syncwarp();
     }
-    old = __shfl_sync(0xffffffffu, old, leader);
-    dr[i] = (d << 16) | (old + below_incl - 1);
-    __syncwarp();
-  }
+}
   __syncthreads();
   after_load();  // every thread holds its keys in registers: the staging buffer is free
 
@@ -209,10 +229,14 @@ __device__ __forceinline__ void sweep_tile(SweepSmem& S, const uint32_t* __restr
   uint32_t count = 0, real = 0, start = 0;
   const unsigned long long tag = ((unsigned long long)pass << kPassShift);
   if (tid < kRadix) {
+    if (UNSTABLE) {
+      count = S.warp_hist[0][tid];  // padding keys were never counted
+    } else {
 #pragma unroll
-    for (int wv = 0; wv < kSortWarps; ++wv) count += S.warp_hist[wv][tid];
+      for (int wv = 0; wv < kSortWarps; ++wv) count += S.warp_hist[wv][tid];
+    }
     real = count;
-    if (!FULL && tid == kRadix - 1) real -= (kTile - n_valid);  // drop the padding keys
+    if (!UNSTABLE && !FULL && tid == kRadix - 1) real -= (kTile - n_valid);  // drop the padding keys
     st_lookback(lookback + (size_t)tile * kRadix + tid, (kStAggregate << kStatusShift) | tag | real);
 
     // exclusive scan of `count` over the 256 digits -> tile_start
@@ -229,12 +253,14 @@ __device__ __forceinline__ void sweep_tile(SweepSmem& S, const uint32_t* __restr
     start = base + inc - count;
     S.tile_start[tid] = start;
     // warp_hist[w][d] := tile position of the first key of (warp w, digit d)
-    uint32_t run = start;
+    if (!UNSTABLE) {
+      uint32_t run = start;
 #pragma unroll
-    for (int wv = 0; wv < kSortWarps; ++wv) {
-      const uint32_t c = S.warp_hist[wv][tid];
-      S.warp_hist[wv][tid] = run;
-      run += c;
+      for (int wv = 0; wv < kSortWarps; ++wv) {
+        const uint32_t c = S.warp_hist[wv][tid];
+        S.warp_hist[wv][tid] = run;
+        run += c;
+      }
     }
   }
   __syncthreads();
@@ -244,7 +270,11 @@ __device__ __forceinline__ void sweep_tile(SweepSmem& S, const uint32_t* __restr
 #pragma unroll
   for (int i = 0; i < kItems; ++i) {
     const uint32_t d = dr[i] >> 16;
-    S.keys[S.warp_hist[warp][d] + (dr[i] & 0xffffu)] = key[i];
+    if (UNSTABLE) {
+      if (FULL || dr[i] != 0xffffffffu) S.keys[S.tile_start[d] + (dr[i] & 0xffffu)] = key[i];
+    } else {
+      S.keys[S.warp_hist[warp][d] + (dr[i] & 0xffffu)] = key[i];
+    }
   }
 
   if (tid < kRadix) {
@@ -253,7 +283,7 @@ __device__ __forceinline__ void sweep_tile(SweepSmem& S, const uint32_t* __restr
     // trip instead of kLook): when many tiles are in flight the walk back to the last
     // finished one is long, and it is pure latency.
     unsigned long long excl = 0;
-    constexpr int kLook = 8;
+    constexpr int kLook = B200_SORT_LOOK;
     for (int64_t t = (int64_t)tile - 1; t >= 0;) {
       unsigned long long e[kLook];
 #pragma unroll
@@ -315,6 +345,16 @@ __global__ void __launch_bounds__(kSortThreads, kSortBlocksPerSm)
   if (n_dev) n = (size_t)*n_dev;
   if (tile_base >= n) return;  // grid was sized for the capacity, not the actual length
   const uint32_t n_valid = (uint32_t)min((size_t)kTile, n - tile_base);
+  if (pass < 0) {  // first pass, flagged by the host as ~pass: may be unstable
+    pass = ~pass;
+    if (n_valid == kTile)
+      sweep_tile<KT, NM, true, false, NoHook, true>(S, in, out, tile_base, n_valid, tile, pass,
+                                                    digit_base, lookback);
+    else
+      sweep_tile<KT, NM, false, false, NoHook, true>(S, in, out, tile_base, n_valid, tile, pass,
+                                                     digit_base, lookback);
+    return;
+  }
   if (n_valid == kTile)
     sweep_tile<KT, NM, true>(S, in, out, tile_base, n_valid, tile, pass, digit_base, lookback);
   else
@@ -490,6 +530,10 @@ static int sort32(const uint32_t* input, uint32_t* keys, uint32_t* tmp, size_t n
     const char* e = getenv("B200LABS_SORT_PERSIST");
     return e ? atoi(e) != 0 : (B200_SORT_PERSIST_DEFAULT != 0);
   }();
+  static const bool unstable_first = [] {
+    const char* e = getenv("B200LABS_SORT_UNSTABLE_FIRST");
+    return e ? atoi(e) != 0 : true;
+  }();
   const bool persist = persist_env && nm == 0 && ((((uintptr_t)input) | ((uintptr_t)keys) | ((uintptr_t)tmp)) & 15u) == 0;
   const Kernel pkernel = sort_onesweep_persistent_kernel<KT, 0>;
   static bool attr_set[64] = {false};
@@ -524,8 +568,10 @@ static int sort32(const uint32_t* input, uint32_t* keys, uint32_t* tmp, size_t n
       pkernel<<<(unsigned)grid, kSortThreads, sizeof(SweepSmemPersistent), st>>>(
           src, dst, n, n_dev, pass, sc.hist + pass * kRadix, sc.lookback, sc.tickets + pass);
     } else {
+      // the first pass need not be stable (nothing to preserve yet): flagged as ~pass
       kernel<<<(unsigned)sc.tiles, kSortThreads, sizeof(SweepSmem), st>>>(
-          src, dst, n, n_dev, pass, sc.hist + pass * kRadix, sc.lookback, sc.tickets + pass);
+          src, dst, n, n_dev, (pass == 0 && unstable_first) ? ~pass : pass, sc.hist + pass * kRadix,
+          sc.lookback, sc.tickets + pass);
     }
     B200_LAUNCH_OK();
     src = dst;

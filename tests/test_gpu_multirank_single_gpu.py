@@ -6,6 +6,7 @@ import numpy as np
 import pytest
 import torch
 
+from cuda_mpi_openmp_b200 import _native as N
 from cuda_mpi_openmp_b200 import ops
 from cuda_mpi_openmp_b200.models import MahalanobisClassifier, RobertsFilter
 from cuda_mpi_openmp_b200.parallel import LocalPeerGroup, shard_rows
@@ -85,6 +86,15 @@ def test_lab3_cooperative_lut_matches_oracle(cuda_device, world):
         assert np.array_equal(d.cpu().numpy(), want[a:b]), r
     torch.cuda.synchronize()
     assert torch.equal(luts[0].local, luts[world - 1].local)
+    # big band: the two-level image pass (colour-cell table in shared memory) against the one-level pass
+    big = torch.randint(-2 ** 31, 2 ** 31 - 1, (2048, 2304), dtype=torch.int32, device=cuda_device)
+    one, two = big.clone(), big.clone()
+    coarse = torch.empty(int(N.lib().b200_lab3_coarse_bytes()), dtype=torch.uint8, device=cuda_device)
+    S.apply_lut(one, luts[0].local_ptr)
+    S.apply_lut(two, luts[world - 1].local_ptr, coarse)
+    assert torch.equal(one, two)
+    assert torch.equal((one.view(torch.uint8).reshape(2048, 2304, 4)[..., 3].long()),
+                       luts[0].local.long()[(big & 0xFFFFFF).long()])
     for b in luts:
         b.free()
 
