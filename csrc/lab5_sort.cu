@@ -115,6 +115,7 @@ __global__ void sort_scan_kernel(unsigned long long* __restrict__ hist, int pass
 constexpr unsigned long long kStatusShift = 62, kPassShift = 58;
 constexpr unsigned long long kValueMask = (1ull << kPassShift) - 1;
 constexpr unsigned long long kStAggregate = 1, kStInclusive = 2;
+constexpr int kGroupTiles = 16;  // look-back groups: [tiles][256] entries, then [groups][256]
 
 __device__ __forceinline__ unsigned long long ld_lookback(const unsigned long long* p) {
   unsigned long long v;
@@ -157,7 +158,8 @@ __device__ __forceinline__ void sweep_tile(SweepSmem& S, const uint32_t* __restr
                                            uint32_t n_valid, uint32_t tile, int pass,
                                            const unsigned long long* __restrict__ digit_base,
                                            unsigned long long* __restrict__ lookback,
-                                           const uint32_t* staged = nullptr, Hook after_load = Hook()) {
+                                           const uint32_t* staged = nullptr, Hook after_load = Hook(),
+                                           unsigned long long* __restrict__ group_lb = nullptr) {
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int shift = pass * kRadixBits;
 
@@ -280,31 +282,56 @@ __device__ __forceinline__ void sweep_tile(SweepSmem& S, const uint32_t* __restr
   if (tid < kRadix) {
     // decoupled look-back: sum aggregates of earlier tiles until an inclusive one.
     // kLook predecessors are probed per round with independent loads (one L2 round
-    // trip instead of kLook): when many tiles are in flight the walk back to the last
-    // finished one is long, and it is pure latency.
+    // trip instead of kLook).  With ~300 tiles in flight the walk back to the last
+    // finished tile was ~95 entries = 12 dependent L2 round trips per tile (a third of
+    // all warp time, profiles/ncu_prof_lab5_v3.md), so the walk is two-level: entries
+    // of my own group of kGroupTiles tiles first, then one entry per earlier GROUP (the
+    // last tile of a group publishes the group's aggregate, later its inclusive sum).
     unsigned long long excl = 0;
     constexpr int kLook = B200_SORT_LOOK;
-    for (int64_t t = (int64_t)tile - 1; t >= 0;) {
-      unsigned long long e[kLook];
+    // walks arr[from], arr[from-1], ... arr[lo]; true when it ended on an inclusive entry
+    auto walk = [&](const unsigned long long* arr, int64_t from, int64_t lo) -> bool {
+      bool inclusive = false;
+      for (int64_t t = from; t >= lo;) {
+        unsigned long long e[kLook];
 #pragma unroll
-      for (int j = 0; j < kLook; ++j)
-        e[j] = (t - j >= 0) ? ld_lookback(lookback + (size_t)(t - j) * kRadix + tid) : 0ull;
-      bool done = false;
+        for (int j = 0; j < kLook; ++j)
+          e[j] = (t - j >= lo) ? ld_lookback(arr + (size_t)(t - j) * kRadix + tid) : 0ull;
+        bool done = false;
 #pragma unroll
-      for (int j = 0; j < kLook; ++j) {
-        if (done || t < 0) continue;
-        const unsigned long long st = e[j] >> kStatusShift;
-        if (st == 0 || ((e[j] >> kPassShift) & 0xf) != (unsigned long long)pass) {
-          done = true;  // not published yet: probe again from this tile
-          continue;
-        }
-        excl += e[j] & kValueMask;
-        --t;
-        if (st == kStInclusive) {
-          t = -1;
-          done = true;
+        for (int j = 0; j < kLook; ++j) {
+          if (done || t < lo) continue;
+          const unsigned long long st = e[j] >> kStatusShift;
+          if (st == 0 || ((e[j] >> kPassShift) & 0xf) != (unsigned long long)pass) {
+            done = true;  // not published yet: probe again from this entry
+            continue;
+          }
+          excl += e[j] & kValueMask;
+          --t;
+          if (st == kStInclusive) {
+            inclusive = true;
+            t = lo - 1;
+            done = true;
+          }
         }
       }
+      return inclusive;
+    };
+    if (group_lb == nullptr) {
+      walk(lookback, (int64_t)tile - 1, 0);
+    } else {
+      const int64_t grp = tile / kGroupTiles, grp_begin = grp * kGroupTiles;
+      const bool group_end = (tile % kGroupTiles) == kGroupTiles - 1;
+      if (!walk(lookback, (int64_t)tile - 1, grp_begin)) {
+        // excl = sum of my group's earlier aggregates
+        if (group_end)
+          st_lookback(group_lb + (size_t)grp * kRadix + tid,
+                      (kStAggregate << kStatusShift) | tag | (excl + real));
+        walk(group_lb, grp - 1, 0);
+      }
+      if (group_end)
+        st_lookback(group_lb + (size_t)grp * kRadix + tid,
+                    (kStInclusive << kStatusShift) | tag | (excl + real));
     }
     st_lookback(lookback + (size_t)tile * kRadix + tid,
                 (kStInclusive << kStatusShift) | tag | (excl + real));
@@ -342,6 +369,8 @@ __global__ void __launch_bounds__(kSortThreads, kSortBlocksPerSm)
   __syncthreads();
   const uint32_t tile = S.tile_id;
   const size_t tile_base = (size_t)tile * kTile;
+  // the grid is one CTA per tile of the capacity; the group entries follow the tile entries
+  unsigned long long* group_lb = lookback + (size_t)gridDim.x * kRadix;
   if (n_dev) n = (size_t)*n_dev;
   if (tile_base >= n) return;  // grid was sized for the capacity, not the actual length
   const uint32_t n_valid = (uint32_t)min((size_t)kTile, n - tile_base);
@@ -349,16 +378,18 @@ __global__ void __launch_bounds__(kSortThreads, kSortBlocksPerSm)
     pass = ~pass;
     if (n_valid == kTile)
       sweep_tile<KT, NM, true, false, NoHook, true>(S, in, out, tile_base, n_valid, tile, pass,
-                                                    digit_base, lookback);
+                                                    digit_base, lookback, nullptr, NoHook(), group_lb);
     else
       sweep_tile<KT, NM, false, false, NoHook, true>(S, in, out, tile_base, n_valid, tile, pass,
-                                                     digit_base, lookback);
+                                                     digit_base, lookback, nullptr, NoHook(), group_lb);
     return;
   }
   if (n_valid == kTile)
-    sweep_tile<KT, NM, true>(S, in, out, tile_base, n_valid, tile, pass, digit_base, lookback);
+    sweep_tile<KT, NM, true>(S, in, out, tile_base, n_valid, tile, pass, digit_base, lookback, nullptr,
+                             NoHook(), group_lb);
   else
-    sweep_tile<KT, NM, false>(S, in, out, tile_base, n_valid, tile, pass, digit_base, lookback);
+    sweep_tile<KT, NM, false>(S, in, out, tile_base, n_valid, tile, pass, digit_base, lookback, nullptr,
+                              NoHook(), group_lb);
 }
 
 // Persistent variant: two CTAs per SM stay resident and pull tiles by ticket; the
@@ -505,6 +536,7 @@ static SortScratch carve(void* scratch, size_t n) {
   s.lookback = (unsigned long long*)p;
   s.tiles = (n + kTile - 1) / kTile;
   p += s.tiles * kRadix * sizeof(unsigned long long);
+  p += ((s.tiles + kGroupTiles - 1) / kGroupTiles) * kRadix * sizeof(unsigned long long);  // group entries
   s.bytes = (size_t)(p - (uint8_t*)scratch);
   return s;
 }
@@ -664,7 +696,7 @@ extern "C" int b200_sort_ex(const void* input, void* keys, void* tmp, size_t n,
 // stream; code under a "no allocation after start-up" rule.  For them this entry
 // point keeps all of that memory in ONE file-scope device array that is part of
 // the library image: it exists on every GPU that loads the library, from load to
-// process exit, and costs B200_SORT_NOALLOC_SCRATCH_BYTES (about 4.3 MB) there.
+// process exit, and costs B200_SORT_NOALLOC_SCRATCH_BYTES (about 4.3 MiB) there.
 //
 //   * at most B200_SORT_NOALLOC_MAX_KEYS (2^20) keys per call; larger n is
 //     rejected with an error, nothing is launched;
@@ -688,7 +720,10 @@ namespace b200 {
 constexpr size_t kNoAllocMaxKeys = B200_SORT_NOALLOC_MAX_KEYS;
 constexpr size_t kNoAllocBookBytes =
     (4 * kRadix * sizeof(unsigned long long) + 64 +
-     ((kNoAllocMaxKeys + kTile - 1) / kTile) * kRadix * sizeof(unsigned long long) + 255) / 256 * 256;
+     ((kNoAllocMaxKeys + kTile - 1) / kTile) * kRadix * sizeof(unsigned long long) +
+     (((kNoAllocMaxKeys + kTile - 1) / kTile + kGroupTiles - 1) / kGroupTiles) * kRadix *
+         sizeof(unsigned long long) +
+     255) / 256 * 256;
 constexpr size_t kNoAllocBytes = kNoAllocBookBytes + kNoAllocMaxKeys * sizeof(uint32_t);
 static_assert(kNoAllocBytes == B200_SORT_NOALLOC_SCRATCH_BYTES || B200_SORT_THREADS != 512,
               "header constant out of date");
