@@ -242,10 +242,13 @@ __global__ void __launch_bounds__(kCountThreads)
 }
 
 // ---------------------------------------------------------- fused partition+exchange
-constexpr int kPartThreads = 256;  // 4 CTAs per SM
+// 512 threads x 2 CTAs per SM.  (256 x 4 was a few percent faster with all eight "ranks"
+// on one GPU, but slower over real NVLink — 3.25 vs 2.9 ms at 8 GPUs: twice the remote
+// reservations and half the run length per destination.)
+constexpr int kPartThreads = 512;
 constexpr int kPartWarps = kPartThreads / 32;
 constexpr int kPartItems = 16;
-constexpr int kPartTile = kPartThreads * kPartItems;  // 4096 keys
+constexpr int kPartTile = kPartThreads * kPartItems;  // 8192 keys
 constexpr int kDestLutBits = 12;
 constexpr uint32_t kDestAmbiguous = 0x80u, kNoDest = 8u;
 
@@ -254,7 +257,7 @@ struct PartTargets {
   unsigned long long* cursor[kMaxWorld];    // their fill cursors (remote atomics)
 };
 
-// One tile = 4096 keys, 16 per thread.  The kernel was ALU-bound when it ranked keys with
+// One tile = 8192 keys, 16 per thread.  The kernel was ALU-bound when it ranked keys with
 // ballots (111 Gkeys/s, profiles/ncu_prof_mgpu.md), so the per-key work is now mostly
 // table look-ups:
 //  * destination: the key range spanned by the splitters is cut into 4096 equal buckets; a
@@ -403,29 +406,24 @@ __global__ void __launch_bounds__(kPartThreads, 1024 / kPartThreads)
           run += (warp_tot[wv][word] >> shf) & 0xffffu;
         }
         tile_total[tid] = run;
-        if (tid < world) {
-          if (phase_mask & 8) {
+        // reserve room in the destination bucket.  The (mostly remote) atomic's result is
+        // not touched until the keys are staged, so its NVLink round trip overlaps staging.
+        if (tid < world && run) {
+          if (phase_mask & 8)
             // my segment in that rank's bucket was reserved by sort_count_reserve_kernel:
-            // sub-allocate it with a LOCAL atomic (no NVLink round trip on the tile's path)
-            if (run) b = atomicAdd(&me->sort_local_cursor[tid], (unsigned long long)run);
-            if (b + run > capacity) b = ~0ull;  // reservation failed earlier (error word is set)
-          } else {
-            if (run) b = atomicAdd_system(s_cursor[tid], (unsigned long long)run);
-            if (b + run > capacity) {
-              atomicOr(&me->error, (unsigned long long)kErrSortOverflow);
-              b = ~0ull;  // poison: this tile's keys for that destination are dropped
-            }
-          }
+            // sub-allocate it with a LOCAL atomic
+            b = atomicAdd(&me->sort_local_cursor[tid], (unsigned long long)run);
+          else
+            b = atomicAdd_system(s_cursor[tid], (unsigned long long)run);
         }
       }
       __syncthreads();
+      uint32_t start = 0;
       if (tid < kMaxWorld) {
-        uint32_t start = 0;
 #pragma unroll
         for (int k = 0; k < kMaxWorld; ++k) start += k < tid ? tile_total[k] : 0u;
 #pragma unroll
         for (int wv = 0; wv < kPartWarps; ++wv) warp_off[wv][tid] = (uint16_t)(warp_off[wv][tid] + start);
-        s_bias[tid] = (tid < world && b != ~0ull) ? s_bucket[tid] + b - start : nullptr;
       }
       __syncthreads();
       // ---- stage keys (and their destination bytes) in destination order
@@ -443,6 +441,15 @@ __global__ void __launch_bounds__(kPartThreads, 1024 / kPartThreads)
             s_dst[pos] = (uint8_t)d;
           }
         }
+      }
+      if (tid < kMaxWorld) {
+        if (tid < world && b + run > capacity) {
+          // overflow (or, with bit 8, a reservation that failed earlier): this tile's keys
+          // for that destination are dropped and the error word says so
+          if (!(phase_mask & 8)) atomicOr(&me->error, (unsigned long long)kErrSortOverflow);
+          b = ~0ull;
+        }
+        s_bias[tid] = (tid < world && b != ~0ull) ? s_bucket[tid] + b - start : nullptr;
       }
       __syncthreads();
       // ---- runs of equal destination leave as contiguous (mostly remote) stores
