@@ -107,6 +107,9 @@ def run_own(args):
 
     rank, world, local_rank = env_world()
     if world > 1:
+        # stdout carries exactly one JSON line: NCCL's own banner ("NCCL version ...", printed
+        # whenever NCCL_DEBUG is set in the environment) goes to stderr instead
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         group = init_distributed()
     else:
         torch.cuda.set_device(0)
