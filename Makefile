@@ -16,6 +16,8 @@ LIBDIR    := cuda_mpi_openmp_b200/lib
 CU_SRCS   := $(wildcard csrc/*.cu)
 CU_OBJS   := $(patsubst csrc/%.cu,$(BUILD)/%.o,$(CU_SRCS))
 CPP_OBJS  := $(BUILD)/oracle.o
+# the stand-alone CPU binaries get the multi-threaded build of the oracles (see csrc/oracle.cpp)
+MT_OBJS  := $(BUILD)/oracle_mt.o
 HDRS      := $(wildcard csrc/*.cuh) include/b200labs.h $(wildcard apps/*.h)
 
 SO        := $(LIBDIR)/libb200labs.so
@@ -40,6 +42,8 @@ $(BUILD)/%.o: csrc/%.cu $(HDRS) | $(BUILD)
 	$(NVCC) $(NVFLAGS) -c $< -o $@
 $(BUILD)/oracle.o: csrc/oracle.cpp include/b200labs.h | $(BUILD)
 	$(CXX) $(CXXFLAGS) -c $< -o $@
+$(BUILD)/oracle_mt.o: csrc/oracle.cpp include/b200labs.h | $(BUILD)
+	$(CXX) $(CXXFLAGS) -DB200_ORACLE_THREADS -pthread -c $< -o $@
 $(BUILD):
 	mkdir -p $(BUILD)
 
@@ -75,24 +79,24 @@ gpu_info/src/gpu_info: apps/gpu_info.cu $(AR_LIB) $(HDRS)
 	$(APP_NV) $< $(AR_LIB) -o $@
 
 # ---- CPU binaries (no CUDA needed: `make cpu` works on any box) ---------------
-APP_CXX := $(CXX) $(CXXFLAGS) -Iapps
-lab1/src/cpu_exe: apps/lab1_cpu.cpp $(CPP_OBJS)
+APP_CXX := $(CXX) $(CXXFLAGS) -pthread -Iapps
+lab1/src/cpu_exe: apps/lab1_cpu.cpp $(MT_OBJS)
 	$(APP_CXX) -DNO_TIME_LINE $^ -o $@
-lab1/src/cpu_exe_to_plot: apps/lab1_cpu.cpp $(CPP_OBJS)
+lab1/src/cpu_exe_to_plot: apps/lab1_cpu.cpp $(MT_OBJS)
 	$(APP_CXX) $^ -o $@
-lab2/src/cpu_exe: apps/lab2_cpu.cpp $(CPP_OBJS)
+lab2/src/cpu_exe: apps/lab2_cpu.cpp $(MT_OBJS)
 	$(APP_CXX) $^ -o $@
-lab3/src/cpu_exe: apps/lab3_cpu.cpp $(CPP_OBJS)
+lab3/src/cpu_exe: apps/lab3_cpu.cpp $(MT_OBJS)
 	$(APP_CXX) $^ -o $@
 lab3/src/test_read_input: apps/lab3_read_input.c
 	$(CC) $(CFLAGS) $< -o $@
-lab5/src/cpu_exe_int: apps/lab5_cpu.cpp $(CPP_OBJS)
+lab5/src/cpu_exe_int: apps/lab5_cpu.cpp $(MT_OBJS)
 	$(APP_CXX) -DKEY_TYPE=0 $^ -o $@
-lab5/src/cpu_exe_float: apps/lab5_cpu.cpp $(CPP_OBJS)
+lab5/src/cpu_exe_float: apps/lab5_cpu.cpp $(MT_OBJS)
 	$(APP_CXX) -DKEY_TYPE=1 $^ -o $@
-lab5/src/cpu_exe_uchar: apps/lab5_cpu.cpp $(CPP_OBJS)
+lab5/src/cpu_exe_uchar: apps/lab5_cpu.cpp $(MT_OBJS)
 	$(APP_CXX) -DKEY_TYPE=2 $^ -o $@
-lab5/src/to_plot_cpu_exe: apps/lab5_cpu.cpp $(CPP_OBJS)
+lab5/src/to_plot_cpu_exe: apps/lab5_cpu.cpp $(MT_OBJS)
 	$(APP_CXX) -DTO_PLOT $^ -o $@
 hw1/src/hw1: apps/hw1.c
 	$(CC) $(CFLAGS) $< -lm -o $@

@@ -2,16 +2,44 @@
 // operation order of the GPU paths.  Used by the CPU binaries and by the tests
 // as the fp reference.  Compile WITHOUT -mfma/-ffast-math: fused operations are
 // spelled out with fmaf()/fma() where (and only where) the GPU code fuses.
+// Built twice: serial for libb200labs (it is loaded into Python processes that manage
+// their own thread pools), and with -DB200_ORACLE_THREADS for the stand-alone CPU
+// binaries, where the element-wise loops are split over std::thread workers — every
+// output element is computed independently, so results do not depend on the thread
+// count.  (std::thread rather than OpenMP: the image has no libgomp development files.)
 #include <algorithm>
 #include <cfloat>
 #include <cmath>
 #include <cstdint>
 #include <cstring>
 #include <vector>
+#ifdef B200_ORACLE_THREADS
+#include <thread>
+#endif
 
 #include "b200labs.h"
 
 namespace {
+
+// f(begin, end) over [0, n) in at most hardware_concurrency() contiguous pieces of >= grain
+template <typename F>
+void parallel_for(int64_t n, int64_t grain, F f) {
+#ifdef B200_ORACLE_THREADS
+  int64_t pieces = n / std::max<int64_t>(grain, 1);
+  if (pieces > 1)  // (hardware_concurrency() reads /sys: tens of microseconds, so only when it can pay)
+    pieces = std::min<int64_t>(pieces, std::max<int64_t>(1, (int64_t)std::thread::hardware_concurrency()));
+  if (pieces > 1) {
+    std::vector<std::thread> workers;
+    for (int64_t k = 1; k < pieces; ++k) workers.emplace_back(f, k * n / pieces, (k + 1) * n / pieces);
+    f(0, n / pieces);
+    for (auto& t : workers) t.join();
+    return;
+  }
+#else
+  (void)grain;
+#endif
+  f(0, n);
+}
 
 struct Px {
   uint8_t r, g, b, a;
@@ -50,30 +78,36 @@ inline uint32_t f32_order_bits(uint32_t u) { return (u & 0x80000000u) ? ~u : (u 
 extern "C" {
 
 void b200_cpu_vecsub_f64(const double* a, const double* b, double* c, size_t n) {
-  for (size_t i = 0; i < n; ++i) c[i] = a[i] - b[i];
+  parallel_for((int64_t)n, 1 << 16, [=](int64_t i0, int64_t i1) {
+    for (int64_t i = i0; i < i1; ++i) c[i] = a[i] - b[i];
+  });
 }
 
 void b200_cpu_roberts(const void* in_, void* out_, int w, int h) {
   const Px* in = (const Px*)in_;
   Px* out = (Px*)out_;
-  std::vector<float> cur(w + 1), nxt(w + 1);
-  auto fill = [&](std::vector<float>& row, int y) {
-    const Px* src = in + (size_t)std::min(y, h - 1) * w;
-    for (int x = 0; x < w; ++x) row[x] = luma(src[x]);
-    row[w] = row[w - 1];  // clamp-to-edge on the right
-  };
   if (w <= 0 || h <= 0) return;
-  fill(cur, 0);
-  for (int y = 0; y < h; ++y) {
-    fill(nxt, y + 1);  // y+1 == h clamps to the last row
-    const Px* src = in + (size_t)y * w;
-    Px* dst = out + (size_t)y * w;
-    for (int x = 0; x < w; ++x) {
-      uint8_t v = roberts_px(cur[x], cur[x + 1], nxt[x], nxt[x + 1]);
-      dst[x] = Px{v, v, v, src[x].a};
+  // rows [y0, y1): luminance rows are computed once and handed down (cur <- nxt)
+  auto band = [&](int y0, int y1) {
+    std::vector<float> cur(w + 1), nxt(w + 1);
+    auto fill = [&](std::vector<float>& row, int y) {
+      const Px* src = in + (size_t)std::min(y, h - 1) * w;
+      for (int x = 0; x < w; ++x) row[x] = luma(src[x]);
+      row[w] = row[w - 1];  // clamp-to-edge on the right
+    };
+    fill(cur, y0);
+    for (int y = y0; y < y1; ++y) {
+      fill(nxt, y + 1);  // y+1 == h clamps to the last row
+      const Px* src = in + (size_t)y * w;
+      Px* dst = out + (size_t)y * w;
+      for (int x = 0; x < w; ++x) {
+        uint8_t v = roberts_px(cur[x], cur[x + 1], nxt[x], nxt[x + 1]);
+        dst[x] = Px{v, v, v, src[x].a};
+      }
+      cur.swap(nxt);
     }
-    cur.swap(nxt);
-  }
+  };
+  parallel_for(h, std::max<int64_t>(1, (1 << 16) / w), [&](int64_t y0, int64_t y1) { band((int)y0, (int)y1); });
 }
 
 void b200_cpu_lab3_stats_ref(const void* img_, int w, const int* pts, const int* class_off,
@@ -175,7 +209,8 @@ void b200_cpu_lab3_finalize(const long long* moments, int nc, double* params) {
 // (ref: lab3/src/main.cu:49-71; DFMA chain checked in SASS).
 void b200_cpu_lab3_classify(void* img_, int64_t npix, int nc, const double* params) {
   Px* img = (Px*)img_;
-  for (int64_t i = 0; i < npix; ++i) {
+  parallel_for(npix, 1 << 12, [=](int64_t i0, int64_t i1) {
+  for (int64_t i = i0; i < i1; ++i) {
     Px px = img[i];
     double best = DBL_MAX;
     int best_c = -1;
@@ -195,6 +230,7 @@ void b200_cpu_lab3_classify(void* img_, int64_t npix, int nc, const double* para
     }
     img[i].a = (uint8_t)best_c;
   }
+  });
 }
 
 void b200_cpu_sort(void* keys, size_t n, int key_type) {
