@@ -50,3 +50,40 @@ def test_lab5_cpu_fixture(built, name, exe, fmt):
 def test_lab2_cpu_error_on_missing_file(built):
     r = subprocess.run([str(built / "lab2/src/cpu_exe")], input="/nonexistent.data\n/tmp/x.data", capture_output=True, text=True)
     assert r.returncode != 0 and "cannot open" in r.stderr
+
+
+def test_threaded_cpu_binaries_match_the_serial_library_oracles(built, lib, tmp_path):
+    """The stand-alone CPU binaries split their loops over std::thread workers above a size
+    threshold (csrc/oracle.cpp, -DB200_ORACLE_THREADS); libb200labs carries the serial build.
+    Inputs big enough to be split must give the same bytes either way."""
+    from cuda_mpi_openmp_b200 import _native as N
+
+    rng = np.random.default_rng(77)
+    # lab2: 301 x 431 px (> 2^16 pixels -> several row bands)
+    h, w = 301, 431
+    img = rng.integers(0, 256, size=(h, w, 4), dtype=np.uint8)
+    src, dst = tmp_path / "in.data", tmp_path / "out.data"
+    src.write_bytes(struct.pack("<ii", w, h) + img.tobytes())
+    run(built / "lab2/src/cpu_exe", f"{src}\n{dst}\n")
+    want = np.empty_like(img)
+    lib.b200_cpu_roberts(N.ptr(img), N.ptr(want), w, h)
+    got = np.frombuffer(dst.read_bytes()[8:], dtype=np.uint8).reshape(h, w, 4)
+    assert np.array_equal(got, want)
+    # lab3: same image, two classes of 40 points each, class byte in alpha
+    pts = [rng.integers(0, [w, h], size=(40, 2)) for _ in range(2)]
+    spec = "\n".join(f"{len(p)} " + " ".join(f"{x} {y}" for x, y in p) for p in pts)
+    dst3 = tmp_path / "out3.data"
+    run(built / "lab3/src/cpu_exe", f"{src}\n{dst3}\n2\n{spec}\n")
+    got3 = np.frombuffer(dst3.read_bytes()[8:], dtype=np.uint8).reshape(h, w, 4)
+    from cuda_mpi_openmp_b200.models import MahalanobisClassifier
+
+    params = MahalanobisClassifier.reference_params(img, pts, mode="host")
+    assert np.array_equal(got3, MahalanobisClassifier.reference_classify(img, params))
+    # lab1: 200k elements (> 2^16 -> several slices)
+    n = 200_000
+    a, b = rng.uniform(-1e100, 1e100, n), rng.uniform(-1e100, 1e100, n)
+    text = f"{n}\n" + " ".join(f"{x:.10e}" for x in a) + "\n" + " ".join(f"{x:.10e}" for x in b) + "\n"
+    out = run(built / "lab1/src/cpu_exe", text)
+    a_p = np.array([float(f"{x:.10e}") for x in a])
+    b_p = np.array([float(f"{x:.10e}") for x in b])
+    assert out.split() == [f"{x:.10e}" for x in (a_p - b_p)]
