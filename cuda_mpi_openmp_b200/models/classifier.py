@@ -13,6 +13,7 @@ import torch
 
 from .. import _native as N
 from ..ops import classify as C
+from ..utils.graphs import GraphedStep
 
 
 class MahalanobisClassifier:
@@ -38,6 +39,22 @@ class MahalanobisClassifier:
 
     def run_device(self, img: torch.Tensor, classes) -> torch.Tensor:
         return self.classify_(img, self.fit(img, classes))
+
+    def graphed(self, img: torch.Tensor, classes) -> GraphedStep:
+        """Statistics + classification of the fixed buffer ``img`` with fixed sample points as ONE
+        CUDA-graph launch (moments, finalize, classify — plus table build and cell table for large
+        images).  Copy a new image into ``img``, call the returned step; the sample points are
+        uploaded here, outside the capture."""
+        if self.stats != "device":
+            raise ValueError("graph capture needs the device statistics path")
+        pts, off = C.pack_points(classes)
+        d_pts, d_off = torch.from_numpy(pts).to(img.device), torch.from_numpy(off).to(img.device)
+        nc = len(classes)
+
+        def step():
+            return self.classify_(img, C.lab3_finalize(C.lab3_moments(img, d_pts, d_off, nc)))
+
+        return GraphedStep(step, device=img.device)
 
     def run_host(self, host_img: torch.Tensor, classes, host_out: torch.Tensor | None = None):
         d = host_img.to(self.device, non_blocking=True)

@@ -6,6 +6,7 @@ import torch
 
 from .. import _native as N
 from ..ops import sort as S
+from ..utils.graphs import GraphedStep
 
 
 class RadixSorter:
@@ -25,6 +26,13 @@ class RadixSorter:
     def run_device(self, keys: torch.Tensor) -> torch.Tensor:
         tmp, scratch = self._workspace(keys)
         return S.sort_(keys, tmp, scratch)
+
+    def graphed(self, keys: torch.Tensor) -> GraphedStep:
+        """The whole sort of the fixed buffer ``keys`` (memset, histogram, scan, four passes) as
+        ONE CUDA-graph launch: copy new keys into ``keys``, call the returned step.  Pays for
+        small arrays, where the seven launches cost more than the kernels."""
+        tmp, scratch = self._workspace(keys)
+        return GraphedStep(lambda: S.sort_(keys, tmp, scratch), device=keys.device)
 
     def run_host(self, host_keys: torch.Tensor, host_out: torch.Tensor | None = None):
         d = host_keys.to(self.device, non_blocking=True)
