@@ -101,7 +101,7 @@ enum { B200_KEY_I32 = 0, B200_KEY_F32 = 1, B200_KEY_U8 = 2, B200_KEY_U32 = 3 };
 size_t b200_sort_scratch_bytes(size_t n, int key_type);
 /* Ascending sort of n keys.  keys is overwritten with the sorted result; tmp
  * is a second buffer of the same size; scratch from b200_sort_scratch_bytes.
- * (The reference ships only lab5/data/*, no program: this lab is new.) */
+ * (The reference ships only the lab5/data files, no program: this lab is new.) */
 int b200_sort(void* keys, void* tmp, size_t n, int key_type, void* scratch,
               size_t scratch_bytes, b200_stream_t s);
 
