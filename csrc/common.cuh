@@ -53,6 +53,23 @@ struct DeviceInfo {
 // cached per device (thread-safe after first call)
 const DeviceInfo& device_info();
 
+// Per-device one-time set-up (cudaFuncSetAttribute and the like).  `f` must be idempotent:
+// two threads racing to be first both run it, which is harmless; nobody skips it.
+struct PerDeviceOnce {
+  std::atomic<bool> done[64];
+  template <typename F>
+  int run(const char* who, F&& f) {
+    int dev = -1;
+    B200_CUDA_OK(cudaGetDevice(&dev));
+    B200_REQUIRE(dev >= 0 && dev < 64, "%s: unexpected device ordinal %d", who, dev);
+    if (!done[dev].load(std::memory_order_acquire)) {
+      if (int rc = f()) return rc;
+      done[dev].store(true, std::memory_order_release);
+    }
+    return 0;
+  }
+};
+
 // ---- device-side PTX wrappers ---------------------------------------------
 #if defined(__CUDACC__)
 

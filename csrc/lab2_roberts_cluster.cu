@@ -110,7 +110,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(cl::kThreads, 1)
     prefetch_tmap(&out_map);
     const int chalf = warp & 1, rgrp = warp >> 1;
     uint8_t* my_out = out_stage + warp * 2 * kOutBytes;
-    int it = 0;
+    int it = 0, n_stores = 0;
     for (int p = cluster_id; p < P.n_pairs; p += n_clusters, ++it) {
       const int s = it % kStages;
       const uint32_t ph = (it / kStages) & 1;
@@ -174,7 +174,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(cl::kThreads, 1)
 
       if (lane == 0) tma_store_wait_read<1>();
       __syncwarp();
-      uint4* ob = (uint4*)(my_out + (it & 1) * kOutBytes) + lane;
+      uint4* ob = (uint4*)(my_out + (n_stores & 1) * kOutBytes) + lane;
       float c0 = luma_rgba(px[0].x), c1 = luma_rgba(px[0].y), c2 = luma_rgba(px[0].z),
             c3 = luma_rgba(px[0].w);
       float c4 = __shfl_down_sync(0xffffffffu, c0, 1);
@@ -198,9 +198,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(cl::kThreads, 1)
       fence_proxy_async_smem();
       __syncwarp();
       if (lane == 0) {
-        tma_store_2d(&out_map, my_out + (it & 1) * kOutBytes, tx * kTileW + chalf * kSubW, (int)y0);
+        tma_store_2d(&out_map, my_out + (n_stores & 1) * kOutBytes, tx * kTileW + chalf * kSubW, (int)y0);
         tma_store_commit();
       }
+      ++n_stores;  // staging halves alternate per store ISSUED (skipped tiles store nothing)
     }
     if (lane == 0) tma_store_wait<0>();
   }
@@ -260,14 +261,13 @@ int roberts_cluster_launch(const void* in, void* out, int w, int64_t h_local,
   const int64_t n_pairs = (int64_t)P.pairs_x * ((h_local + kTileH - 1) / kTileH);
   B200_REQUIRE(n_pairs < (1ll << 30), "roberts_cluster: too many tiles");
   P.n_pairs = (int)n_pairs;
-  static bool attr_set[64] = {false};
-  int dev = 0;
-  cudaGetDevice(&dev);
-  if (!attr_set[dev & 63]) {
+  static PerDeviceOnce attr_once;
+  if (int rc = attr_once.run("roberts_cluster", [&]() -> int {
     B200_CUDA_OK(cudaFuncSetAttribute(roberts_cluster_kernel,
                                       cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
-    attr_set[dev & 63] = true;
-  }
+        return 0;
+      }))
+    return rc;
   int64_t clusters = device_info().sm_count / 2;
   if (clusters > n_pairs) clusters = n_pairs;
   roberts_cluster_kernel<<<(int)clusters * 2, kThreads, kSmemBytes, st>>>(main_map, sliver_map,

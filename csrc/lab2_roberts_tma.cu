@@ -117,6 +117,11 @@ __global__ void __launch_bounds__(kTmaThreads, 1)
   const int rgrp = warp >> 1;       // rows rgrp*4 .. rgrp*4+3
   uint8_t* my_out = out_stage + warp * 2 * kOutBytes;
   int it = 0;
+  // The staging half is picked by the number of stores this warp has ISSUED, not by the
+  // tile counter: a warp skips tiles whose block lies outside the image without storing,
+  // and "wait until at most one store group is still reading" only protects the buffer
+  // used two STORES ago.
+  int n_stores = 0;
   for (int64_t t = blockIdx.x; t < P.n_tiles; t += gridDim.x, ++it) {
     const int s = it % kStages;
     const uint32_t ph = (it / kStages) & 1;
@@ -165,10 +170,10 @@ __global__ void __launch_bounds__(kTmaThreads, 1)
     __syncwarp();
     if (lane == 0) mbar_arrive(&empty[s]);
 
-    // staging buffer (it & 1) was handed to the TMA store two tiles ago
+    // staging buffer (n_stores & 1) was handed to the TMA store two stores ago
     if (lane == 0) tma_store_wait_read<1>();
     __syncwarp();
-    uint4* ob = (uint4*)(my_out + (it & 1) * kOutBytes) + lane;
+    uint4* ob = (uint4*)(my_out + (n_stores & 1) * kOutBytes) + lane;
 
     float c0 = luma_rgba(px[0].x), c1 = luma_rgba(px[0].y), c2 = luma_rgba(px[0].z),
           c3 = luma_rgba(px[0].w);
@@ -193,9 +198,10 @@ __global__ void __launch_bounds__(kTmaThreads, 1)
     fence_proxy_async_smem();  // generic-proxy writes -> visible to the TMA engine
     __syncwarp();
     if (lane == 0) {
-      tma_store_2d(&out_map, my_out + (it & 1) * kOutBytes, tx * kTileW + chalf * kSubW, (int)y0);
+      tma_store_2d(&out_map, my_out + (n_stores & 1) * kOutBytes, tx * kTileW + chalf * kSubW, (int)y0);
       tma_store_commit();
     }
+    ++n_stores;
   }
   if (lane == 0) tma_store_wait<0>();
 }
@@ -265,14 +271,13 @@ int roberts_tma_launch(const void* in, void* out, int w, int64_t h_local, const 
     return e ? atoi(e) : 0;
   }();
   P.l2_hints = hints;
-  static bool attr_set[64] = {false};
-  int dev = 0;
-  cudaGetDevice(&dev);
-  if (!attr_set[dev & 63]) {
+  static PerDeviceOnce attr_once;
+  if (int rc = attr_once.run("roberts_tma", [&]() -> int {
     B200_CUDA_OK(cudaFuncSetAttribute(roberts_tma_kernel,
                                       cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
-    attr_set[dev & 63] = true;
-  }
+        return 0;
+      }))
+    return rc;
   int64_t grid = device_info().sm_count;
   if (grid > P.n_tiles) grid = P.n_tiles;
   roberts_tma_kernel<<<(int)grid, kTmaThreads, kSmemBytes, st>>>(in_map, halo_map, out_map, P);

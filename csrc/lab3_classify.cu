@@ -257,15 +257,14 @@ static int run_lut_apply(uint32_t* img, int64_t npix, const uint8_t* lut, uint8_
   const bool two_level = coarse && !coarse_off && (((uintptr_t)coarse) & 15u) == 0 &&
                          n_vec >= (int64_t(1) << 20);
   if (n_vec && two_level) {
-    static bool attr_set[64] = {false};
-    int dev = 0;
-    cudaGetDevice(&dev);
-    if (!attr_set[dev & 63]) {
+    static PerDeviceOnce attr_once;
+    if (int rc = attr_once.run("lab3", [&]() -> int {
       B200_CUDA_OK(cudaFuncSetAttribute(lab3_lut_apply_coarse_kernel<4>,
                                         cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         (int)kCoarseBytes));
-      attr_set[dev & 63] = true;
-    }
+          return 0;
+        }))
+      return rc;
     lab3_lut_coarsen_kernel<<<(unsigned)(kCoarseBytes / 256), 256, 0, st>>>((const uint32_t*)lut,
                                                                            coarse);
     B200_LAUNCH_OK();
@@ -352,15 +351,14 @@ extern "C" int b200_lab3_classify(void* img, int64_t npix, int nc, const double*
       lab3_lut_build_kernel<<<(1 << 22) / kClsThreads, kClsThreads, 0, st>>>((uint32_t*)scratch, nc,
                                                                              params);
     } else {
-      static bool attr_set[64] = {false};
-      int dev = 0;
-      cudaGetDevice(&dev);
-      if (!attr_set[dev & 63]) {
+      static PerDeviceOnce attr_once;
+      if (int rc = attr_once.run("lab3", [&]() -> int {
         B200_CUDA_OK(cudaFuncSetAttribute(lab3_lut_build_hoisted_kernel,
                                           cudaFuncAttributeMaxDynamicSharedMemorySize,
                                           (int)sizeof(LutSmem)));
-        attr_set[dev & 63] = true;
-      }
+            return 0;
+          }))
+        return rc;
       lab3_lut_build_hoisted_kernel<<<256 * (256 / kLutR), kLutThreads, sizeof(LutSmem), st>>>(
           (uint8_t*)scratch, nc, params);
     }

@@ -467,6 +467,236 @@ __global__ void __launch_bounds__(kSortThreads, kSortBlocksPerSm)
   }
 }
 
+// ------------------------------------------------------------------ pass kernel, second generation
+// What the profile of the kernel above said (profiles/ncu_prof_lab5_v4.md): 60 warp
+// instructions per 32 keys, issue slots 44% busy, 5.8 warps per issue parked on a CTA
+// barrier, two CTAs per SM.  This kernel does the same job (one ticketed tile, look-back,
+// coalesced runs out) with
+//   * an EARLY COUNT: every key first bumps its (warp, digit) counter, so the tile's digit
+//     counts exist before any ranking; the digit threads turn them into tile positions and
+//     publish the tile aggregate right away (successor tiles never wait for our ranking);
+//   * ranking that writes each key straight to its tile position (no rank registers, no
+//     second staging loop): lanes with equal digits find each other through ONE 64-bit
+//     shared word per (warp, digit) - low half = lane mask of the current row (atomicOr),
+//     high half = next free tile position - read with one LDS.64 and rewritten by the
+//     group's highest lane with one STS.64 (which also clears the mask for the next row);
+//   * keys kept in their ordered (unsigned-comparable) form between passes: the first
+//     pass converts on load, the last one converts back on store, the two in the middle
+//     extract a digit with a single byte-permute;
+//   * 40 registers, three CTAs (48 warps) per SM.
+struct PassSmem {
+  uint32_t keys[kTile];                         // 32 KB: keys in digit order
+  unsigned long long pair[kSortWarps][kRadix];  // 32 KB: {lane mask of the row, next tile position}
+  unsigned long long global_off[kRadix];        // byte address in `out` of (digit, tile position 0)
+  uint32_t scan_tmp[kRadix / 32];
+  uint32_t tile_id;
+};
+#ifndef B200_SORT_PASS_BLOCKS
+#define B200_SORT_PASS_BLOCKS 3
+#endif
+
+// one 64-bit shared-memory access for a {mask, position} word (never cached in registers)
+__device__ __forceinline__ uint2 lds_pair(const unsigned long long* p) {
+  uint2 v;
+  asm volatile("ld.volatile.shared.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(smem_u32(p)) : "memory");
+  return v;
+}
+__device__ __forceinline__ void sts_pair(unsigned long long* p, uint32_t lo, uint32_t hi) {
+  asm volatile("st.volatile.shared.v2.u32 [%0], {%1, %2};" ::"r"(smem_u32(p)), "r"(lo), "r"(hi) : "memory");
+}
+
+template <int KT>
+__device__ __forceinline__ uint32_t from_ordered(uint32_t o) {
+  if (KT == B200_KEY_I32) return o ^ 0x80000000u;
+  if (KT == B200_KEY_F32) return (o & 0x80000000u) ? (o ^ 0x80000000u) : ~o;
+  return o;
+}
+
+template <int KT, bool FIRST, bool LAST, bool FULL>
+__device__ __forceinline__ void pass_tile(PassSmem& S, const uint32_t* __restrict__ in,
+                                          uint32_t* __restrict__ out, size_t tile_base,
+                                          uint32_t n_valid, uint32_t tile, int pass,
+                                          const unsigned long long* __restrict__ digit_base,
+                                          unsigned long long* __restrict__ lookback,
+                                          unsigned long long* __restrict__ group_lb) {
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const uint32_t sel = 0x4440u | (uint32_t)pass;  // byte `pass` of the key -> bits 0..7
+  const uint32_t w_off = warp * (kItems * 32) + lane;
+  unsigned long long* pr = S.pair[warp];
+  uint32_t* pr_hi = reinterpret_cast<uint32_t*>(pr) + 1;  // high words, stride 2
+
+  // ---- load (warp-striped: logical order == memory order) + early count
+  uint32_t key[kItems];
+  uint32_t rk[FIRST ? kItems : 1];
+#pragma unroll
+  for (int i = 0; i < kItems; ++i) {
+    const uint32_t o = w_off + i * 32;
+    uint32_t k = (FULL || o < n_valid) ? ld_stream_u32(in + tile_base + o) : 0xffffffffu;
+    if (FIRST) k = to_ordered<KT>(k);
+    key[i] = k;
+  }
+#pragma unroll
+  for (int i = 0; i < kItems; ++i) {
+    const uint32_t d = __byte_perm(key[i], 0, sel);
+    if (FULL || (w_off + i * 32) < n_valid) {
+      // the first pass has no earlier order to keep: the counter's old value IS the rank
+      if (FIRST) rk[i] = atomicAdd(&pr_hi[2 * d], 1u);
+      else atomicAdd(&pr_hi[2 * d], 1u);
+    }
+  }
+  __syncthreads();
+
+  // ---- digit threads: counts -> tile positions, publish the aggregate, scan the digits
+  uint32_t count = 0, start = 0;
+  const unsigned long long tag = ((unsigned long long)pass << kPassShift);
+  if (tid < kRadix) {
+    uint32_t* col = reinterpret_cast<uint32_t*>(&S.pair[0][tid]) + 1;
+#pragma unroll
+    for (int wv = 0; wv < kSortWarps; ++wv) count += col[wv * kRadix * 2];
+    st_lookback(lookback + (size_t)tile * kRadix + tid, (kStAggregate << kStatusShift) | tag | count);
+    uint32_t inc = count;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+      if (lane >= o) inc += t;
+    }
+    if (lane == 31) S.scan_tmp[warp] = inc;
+    asm volatile("bar.sync 1, 256;" ::: "memory");  // the kRadix digit threads only
+    uint32_t base = 0;
+    for (int wv = 0; wv < warp; ++wv) base += S.scan_tmp[wv];
+    start = base + inc - count;
+    uint32_t run = start;
+#pragma unroll
+    for (int wv = 0; wv < kSortWarps; ++wv) {
+      const uint32_t c = col[wv * kRadix * 2];
+      col[wv * kRadix * 2] = run;  // first tile position of (warp wv, digit tid)
+      run += c;
+    }
+  }
+  __syncthreads();
+
+  // ---- rank + place
+  if (FIRST) {
+#pragma unroll
+    for (int i = 0; i < kItems; ++i) {
+      const uint32_t d = __byte_perm(key[i], 0, sel);
+      if (FULL || (w_off + i * 32) < n_valid) S.keys[pr_hi[2 * d] + rk[i]] = key[i];
+    }
+  } else {
+    const uint32_t lane_bit = 1u << lane;
+    const uint32_t le_mask = 0xffffffffu >> (31 - lane);
+#pragma unroll
+    for (int i = 0; i < kItems; ++i) {
+      const uint32_t d = __byte_perm(key[i], 0, sel);
+      const bool valid = FULL || (w_off + i * 32) < n_valid;
+      if (valid) atomicOr(reinterpret_cast<uint32_t*>(&pr[d]), lane_bit);
+      __syncwarp();
+      uint2 v = make_uint2(0u, 0u);  // {lanes of this row with my digit, next free position}
+      if (valid) v = lds_pair(&pr[d]);
+      __syncwarp();
+      // on the group's highest lane `next` is the position after the whole group
+      const uint32_t next = v.y + __popc(v.x & le_mask);
+      if (valid) {
+        if ((v.x >> lane) == 1u) sts_pair(&pr[d], 0u, next);
+        S.keys[next - 1] = key[i];
+      }
+      __syncwarp();
+    }
+  }
+
+  // ---- digit threads: decoupled look-back (two-level, see sweep_tile)
+  if (tid < kRadix) {
+    unsigned long long excl = 0;
+    constexpr int kLook = B200_SORT_LOOK;
+    auto walk = [&](const unsigned long long* arr, int64_t from, int64_t lo) -> bool {
+      bool inclusive = false;
+      for (int64_t t = from; t >= lo;) {
+        unsigned long long e[kLook];
+#pragma unroll
+        for (int j = 0; j < kLook; ++j)
+          e[j] = (t - j >= lo) ? ld_lookback(arr + (size_t)(t - j) * kRadix + tid) : 0ull;
+        bool done = false;
+#pragma unroll
+        for (int j = 0; j < kLook; ++j) {
+          if (done || t < lo) continue;
+          const unsigned long long st = e[j] >> kStatusShift;
+          if (st == 0 || ((e[j] >> kPassShift) & 0xf) != (unsigned long long)pass) {
+            done = true;
+            continue;
+          }
+          excl += e[j] & kValueMask;
+          --t;
+          if (st == kStInclusive) {
+            inclusive = true;
+            t = lo - 1;
+            done = true;
+          }
+        }
+      }
+      return inclusive;
+    };
+    const int64_t grp = tile / kGroupTiles, grp_begin = grp * kGroupTiles;
+    const bool group_end = (tile % kGroupTiles) == kGroupTiles - 1;
+    if (!walk(lookback, (int64_t)tile - 1, grp_begin)) {
+      if (group_end)
+        st_lookback(group_lb + (size_t)grp * kRadix + tid,
+                    (kStAggregate << kStatusShift) | tag | (excl + count));
+      walk(group_lb, grp - 1, 0);
+    }
+    if (group_end)
+      st_lookback(group_lb + (size_t)grp * kRadix + tid,
+                  (kStInclusive << kStatusShift) | tag | (excl + count));
+    st_lookback(lookback + (size_t)tile * kRadix + tid,
+                (kStInclusive << kStatusShift) | tag | (excl + count));
+    S.global_off[tid] =
+        (unsigned long long)(uintptr_t)out + 4ull * (digit_base[tid] + excl - start);
+  }
+  __syncthreads();
+
+  // ---- coalesced runs out
+#pragma unroll
+  for (int i = 0; i < kItems; ++i) {
+    const uint32_t p = tid + i * kSortThreads;
+    if (FULL || p < n_valid) {
+      const uint32_t k = S.keys[p];
+      const uint32_t d = __byte_perm(k, 0, sel);
+      uint32_t* dst = reinterpret_cast<uint32_t*>((uintptr_t)(S.global_off[d] + 4ull * p));
+      *dst = LAST ? from_ordered<KT>(k) : k;
+    }
+  }
+}
+
+template <int KT, bool FIRST, bool LAST, int BLOCKS = B200_SORT_PASS_BLOCKS>
+__global__ void __launch_bounds__(kSortThreads, BLOCKS)
+    sort_pass_kernel(const uint32_t* __restrict__ in, uint32_t* __restrict__ out, size_t n,
+                     const unsigned long long* __restrict__ n_dev, int pass,
+                     const unsigned long long* __restrict__ digit_base /*[256]*/,
+                     unsigned long long* __restrict__ lookback /*[tiles][256] then [groups][256]*/,
+                     uint32_t* __restrict__ ticket) {
+  extern __shared__ __align__(16) uint8_t smem_raw[];
+  PassSmem& S = *reinterpret_cast<PassSmem*>(smem_raw);
+  const int tid = threadIdx.x;
+  if (tid == 0) S.tile_id = atomicAdd(ticket, 1u);
+  {  // each warp clears its own 2 KB of counter words
+    uint4* z = reinterpret_cast<uint4*>(S.pair[tid >> 5]);
+#pragma unroll
+    for (int j = 0; j < kRadix * 8 / 16 / 32; ++j) z[(tid & 31) + 32 * j] = make_uint4(0, 0, 0, 0);
+  }
+  __syncthreads();
+  const uint32_t tile = S.tile_id;
+  const size_t tile_base = (size_t)tile * kTile;
+  unsigned long long* group_lb = lookback + (size_t)gridDim.x * kRadix;
+  if (n_dev) n = (size_t)*n_dev;
+  if (tile_base >= n) return;  // grid was sized for the capacity, not the actual length
+  const uint32_t n_valid = (uint32_t)min((size_t)kTile, n - tile_base);
+  if (n_valid == kTile)
+    pass_tile<KT, FIRST, LAST, true>(S, in, out, tile_base, n_valid, tile, pass, digit_base, lookback,
+                                     group_lb);
+  else
+    pass_tile<KT, FIRST, LAST, false>(S, in, out, tile_base, n_valid, tile, pass, digit_base,
+                                      lookback, group_lb);
+}
+
 // ------------------------------------------------------------------ uint8 keys
 __global__ void __launch_bounds__(kHistThreads)
     sort_u8_hist_kernel(const uint8_t* __restrict__ keys, size_t n,
@@ -568,16 +798,33 @@ static int sort32(const uint32_t* input, uint32_t* keys, uint32_t* tmp, size_t n
   }();
   const bool persist = persist_env && nm == 0 && ((((uintptr_t)input) | ((uintptr_t)keys) | ((uintptr_t)tmp)) & 15u) == 0;
   const Kernel pkernel = sort_onesweep_persistent_kernel<KT, 0>;
-  static bool attr_set[64] = {false};
-  int dev = 0;
-  cudaGetDevice(&dev);
-  if (!attr_set[dev & 63]) {
+  // B200LABS_SORT_IMPL=4 selects the first-generation pass kernel (kept for A/B timing)
+  static const int impl = [] {
+    const char* e = getenv("B200LABS_SORT_IMPL");
+    return e ? atoi(e) : 5;
+  }();
+  static const int pass_blocks = [] {  // CTAs per SM the pass kernel is compiled for (2: 64 registers)
+    const char* e = getenv("B200LABS_SORT_BLOCKS");
+    return e ? atoi(e) : B200_SORT_PASS_BLOCKS;
+  }();
+  const Kernel pass_first = pass_blocks == 2 ? sort_pass_kernel<KT, true, false, 2> : sort_pass_kernel<KT, true, false>;
+  const Kernel pass_mid = pass_blocks == 2 ? sort_pass_kernel<KT, false, false, 2> : sort_pass_kernel<KT, false, false>;
+  const Kernel pass_last = pass_blocks == 2 ? sort_pass_kernel<KT, false, true, 2> : sort_pass_kernel<KT, false, true>;
+  static PerDeviceOnce attr_once;
+  if (int rc = attr_once.run("sort", [&]() -> int {
+    // idempotent, so two threads racing to be first is harmless
     B200_CUDA_OK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                       (int)sizeof(SweepSmem)));
     B200_CUDA_OK(cudaFuncSetAttribute(pkernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                       (int)sizeof(SweepSmemPersistent)));
-    attr_set[dev & 63] = true;
-  }
+    for (Kernel k : {pass_first, pass_mid, pass_last}) {
+      B200_CUDA_OK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        (int)sizeof(PassSmem)));
+      B200_CUDA_OK(cudaFuncSetAttribute(k, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+    }
+        return 0;
+      }))
+    return rc;
   {
     size_t want = (n / 4 + kHistThreads - 1) / kHistThreads + 1;
     // >= sms*8 blocks and <= 2^22 keys per block (32-bit shared counters stay exact)
@@ -594,7 +841,11 @@ static int sort32(const uint32_t* input, uint32_t* keys, uint32_t* tmp, size_t n
   const uint32_t* src = input;
   uint32_t* dst = tmp;
   for (int pass = 0; pass < 4; ++pass) {
-    if (persist) {
+    if (impl >= 5) {
+      const Kernel k = pass == 0 ? pass_first : pass == 3 ? pass_last : pass_mid;
+      k<<<(unsigned)sc.tiles, kSortThreads, sizeof(PassSmem), st>>>(
+          src, dst, n, n_dev, pass, sc.hist + pass * kRadix, sc.lookback, sc.tickets + pass);
+    } else if (persist) {
       size_t grid = (size_t)sms * kSortBlocksPerSm;
       if (grid > sc.tiles) grid = sc.tiles;
       pkernel<<<(unsigned)grid, kSortThreads, sizeof(SweepSmemPersistent), st>>>(

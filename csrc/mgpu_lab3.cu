@@ -206,14 +206,13 @@ extern "C" int b200_lab3_lut_build_allgather(void* const* lut_ptrs, int nc, cons
   for (int p = 0; p < kMaxWorld; ++p) tg.lut[p] = p < world ? (uint8_t*)lut_ptrs[p] : nullptr;
   SymmPeers peers{(SymmWorkspace* const*)ws_ptrs};
   B200_REQUIRE((256 / world) % kLutBGroup == 0, "lab3: world %d leaves fewer than 8 B values per rank", world);
-  static bool attr_set[64] = {false};
-  int dev = 0;
-  cudaGetDevice(&dev);
-  if (!attr_set[dev & 63]) {
+  static PerDeviceOnce attr_once;
+  if (int rc = attr_once.run("lab3_mgpu", [&]() -> int {
     B200_CUDA_OK(cudaFuncSetAttribute(lab3_lut_build_allgather_kernel,
                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(LutSmem)));
-    attr_set[dev & 63] = true;
-  }
+        return 0;
+      }))
+    return rc;
   const unsigned grid = (phase_mask & 1) ? 256u * (256 / kLutR) : 1u;
   lab3_lut_build_allgather_kernel<<<grid, kLutThreads, sizeof(LutSmem), as_stream(s)>>>(
       tg, nc, params, peers, rank, world, epoch, phase_mask, kDefaultTimeoutNs);

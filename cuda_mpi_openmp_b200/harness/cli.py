@@ -21,14 +21,14 @@ from .processors import LAB_PROCESSORS
 
 
 def build_parser() -> argparse.ArgumentParser:
-    p = argparse.ArgumentParser(description="Run kernel testing with subprocess.")
-    p.add_argument("--binary_path_cuda", type=str, required=True, help="Path to the cuda binary file.")
-    p.add_argument("--binary_path_cpu", type=str, default=None, help="Path to the cpu binary file.")
-    p.add_argument("--k_times", type=int, default=20, help="Number of times to run the kernel.")
-    p.add_argument("--return_inp", action="store_true", help="Return input for binary.")
-    p.add_argument("--return_task_res", action="store_true", help="Return the result of task.")
+    p = argparse.ArgumentParser(description="Black-box timing and verification of a lab binary (one subprocess per run).")
+    p.add_argument("--binary_path_cuda", type=str, required=True, help="CUDA build to test, at <lab>/<dir>/<exe> (the lab is read from the path).")
+    p.add_argument("--binary_path_cpu", type=str, default=None, help="Optional CPU build, timed beside the CUDA one.")
+    p.add_argument("--k_times", type=int, default=20, help="Runs per launch geometry.")
+    p.add_argument("--return_inp", action="store_true", help="Keep each run's stdin text in the result rows.")
+    p.add_argument("--return_task_res", action="store_true", help="Keep each run's parsed output in the result rows.")
     p.add_argument("--kernel_sizes", type=str, default="[[512, 512]]",
-                   help="Kernel sizes in JSON, e.g. '[[1, 32], [512, 512], [1024, 1024]]'")
+                   help="Launch geometries to sweep, JSON list of [size1, size2] (ints or 2-lists)")
     p.add_argument("--metadata_columns2plot", type=str, default="[]",
                    help='Columns listed in the chart legend, JSON, e.g. \'["filename"]\'')
     p.add_argument("--max_parallel", type=int, default=1,

@@ -47,7 +47,7 @@ class MahalanobisClassifier:
         uploaded here, outside the capture."""
         if self.stats != "device":
             raise ValueError("graph capture needs the device statistics path")
-        pts, off = C.pack_points(classes)
+        pts, off = C.pack_points(classes, w=img.shape[1], h=img.shape[0])
         d_pts, d_off = torch.from_numpy(pts).to(img.device), torch.from_numpy(off).to(img.device)
         nc = len(classes)
 
@@ -70,7 +70,7 @@ class MahalanobisClassifier:
     def reference_params(rgba: np.ndarray, classes, mode: str = "moments") -> np.ndarray:
         img = np.ascontiguousarray(rgba, dtype=np.uint8)
         h, w = img.shape[:2]
-        pts, off = C.pack_points(classes)
+        pts, off = C.pack_points(classes, w=w, h=h)
         nc = len(classes)
         params = np.zeros((nc, C.N_PARAMS), dtype=np.float64)
         L = N.lib()

@@ -10,11 +10,22 @@ CLASSIFY_VARIANTS = {"auto": 0, "direct": 1, "lut": 2}
 MAX_CLASSES, N_MOMENTS, N_PARAMS = 32, 10, 12
 
 
-def pack_points(classes) -> tuple[np.ndarray, np.ndarray]:
-    """[(np_c, 2) int arrays of (x, y)] -> flat int32 pts, int32 offsets (nc + 1)."""
+def pack_points(classes, w: int | None = None, h: int | None = None) -> tuple[np.ndarray, np.ndarray]:
+    """[(np_c, 2) int arrays of (x, y)] -> flat int32 pts, int32 offsets (nc + 1).
+
+    With ``w``/``h`` (the WHOLE image, not a band) every point is checked against the image
+    bounds here, once, on the host.  The kernels skip a point outside their band because
+    another band owns it; a point outside the whole image would be skipped by every band
+    and silently vanish from the statistics, so it is an error."""
     if not 1 <= len(classes) <= MAX_CLASSES:
         raise ValueError(f"class count must be 1..{MAX_CLASSES}")
     arrs = [np.asarray(c, dtype=np.int32).reshape(-1, 2) for c in classes]
+    if w is not None and h is not None:
+        for c, a in enumerate(arrs):
+            bad = (a[:, 0] < 0) | (a[:, 0] >= w) | (a[:, 1] < 0) | (a[:, 1] >= h)
+            if bad.any():
+                x, y = a[np.argmax(bad)]
+                raise ValueError(f"class {c}: sample point ({x}, {y}) lies outside the {w}x{h} image")
     off = np.zeros(len(arrs) + 1, dtype=np.int32)
     off[1:] = np.cumsum([a.shape[0] for a in arrs])
     pts = np.concatenate(arrs, axis=0).reshape(-1) if off[-1] else np.zeros(0, np.int32)
@@ -44,7 +55,7 @@ def lab3_finalize(moments: torch.Tensor, params: torch.Tensor | None = None) -> 
 
 
 def lab3_params_from_points(img: torch.Tensor, classes) -> torch.Tensor:
-    pts, off = pack_points(classes)
+    pts, off = pack_points(classes, w=img.shape[1], h=img.shape[0])
     d_pts = torch.from_numpy(pts).to(img.device)
     d_off = torch.from_numpy(off).to(img.device)
     return lab3_finalize(lab3_moments(img, d_pts, d_off, len(classes)))

@@ -94,11 +94,21 @@ class ShardedVectorSub:
 # ------------------------------------------------------------------------- lab2
 class ShardedRoberts:
     """Row-sharded Roberts filter.  The band lives in a symmetric buffer so that rank
-    r-1's kernel can read this band's first row as its halo."""
+    r-1's kernel can read this band's first row as its halo.
 
-    def __init__(self, group: PeerGroup, w: int, h_total: int, impl: str = "fused", variant: str = "auto"):
+    Ordering contract: the fused kernel reads the NEIGHBOUR's band with plain loads and no
+    in-kernel handshake, which is only safe while that band is not being written.  A caller
+    that fills the bands once (the bench) needs one ``group.barrier()`` after the fill.  A
+    caller that refills ``band`` between steps must order "every rank's upload finished"
+    before any rank's ``step()``: pass ``refill_barrier=True`` and ``step()`` runs the
+    stream-ordered cross-GPU barrier (``PeerGroup.device_barrier``, flags over peer memory,
+    no host sync) in front of the kernel, or call ``group.device_barrier()`` yourself."""
+
+    def __init__(self, group: PeerGroup, w: int, h_total: int, impl: str = "fused", variant: str = "auto",
+                 refill_barrier: bool = False):
         assert impl in ("fused", "nccl")
         self.group, self.w, self.h_total, self.impl, self.variant = group, w, h_total, impl, variant
+        self.refill_barrier = refill_barrier
         self.y0, self.y1 = shard_rows(h_total, group.world)[group.rank]
         self.h_local = self.y1 - self.y0
         self.sym_in: SymmetricBuffer = group.alloc(max(1, self.h_local) * w * 4)
@@ -119,6 +129,8 @@ class ShardedRoberts:
     def step(self) -> torch.Tensor:
         g = self.group
         if self.impl == "fused":
+            if self.refill_barrier and g.world > 1:
+                g.device_barrier()          # neighbours' uploads are complete before our loads
             below = self.below_address()
         else:
             dist = g.dist
@@ -187,7 +199,7 @@ class ShardedClassifier:
         self.y0, self.y1 = shard_rows(h_total, group.world)[group.rank]
         self.h_local = self.y1 - self.y0
         self.nc = len(classes)
-        pts, off = CL.pack_points(classes)
+        pts, off = CL.pack_points(classes, w=w, h=h_total)   # checked against the WHOLE image
         dev = group.device
         self.d_pts = torch.from_numpy(pts).to(dev) if pts.size else torch.zeros(2, dtype=torch.int32, device=dev)
         self.d_off = torch.from_numpy(off).to(dev)

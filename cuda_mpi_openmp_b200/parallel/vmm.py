@@ -17,6 +17,8 @@ from __future__ import annotations
 import ctypes as C
 import os
 import socket
+import struct
+import time
 import uuid
 from typing import Dict, List
 
@@ -84,43 +86,76 @@ def exchange_fds(group: PeerGroup, outgoing: Dict[int, List[int]]) -> Dict[int, 
     """Send ``outgoing[dest]`` (file descriptors) to each other rank; returns what the
     other ranks sent here, by sender.  Collective.  Every rank listens on an abstract
     unix socket, the names go round by all_gather_object, then each rank connects and
-    sends — the kernel queues the messages, so nobody needs a second thread."""
+    sends — the kernel queues the messages, so nobody needs a second thread.
+
+    Abstract sockets are reachable by any process in the network namespace, so a message
+    is only accepted when it (a) comes from the pid the sender announced through the
+    process group (SO_PEERCRED), (b) carries the random token this rank handed out in
+    the same all_gather, (c) names a rank that has not delivered yet.  Anything else is
+    dropped (its descriptors closed) and the rank keeps accepting until the deadline.
+    Descriptors received before a failure are closed on the way out."""
     world, rank = group.world, group.rank
     if world == 1:
         return {}
     name = "\0b200vmm-%d-%s" % (os.getpid(), uuid.uuid4().hex)
+    token = uuid.uuid4().bytes                       # 16 random bytes; senders must echo them
     srv = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+    incoming: Dict[int, List[int]] = {}
+    ok = False
     try:
         srv.bind(name)
         srv.listen(world)
-        names: List[str] = [""] * world
-        group.dist.all_gather_object(names, name, group=group.pg)
+        cards: list = [None] * world
+        group.dist.all_gather_object(cards, (name, os.getpid(), token), group=group.pg)
         for dest in range(world):
             if dest == rank:
                 continue
             fds = outgoing.get(dest, [])
             with socket.socket(socket.AF_UNIX, socket.SOCK_STREAM) as c:
-                c.connect(names[dest])
-                header = b"%4d%4d" % (rank, len(fds))
+                c.connect(cards[dest][0])
+                header = cards[dest][2] + b"%4d%4d" % (rank, len(fds))
                 if fds:
                     socket.send_fds(c, [header], fds)
                 else:
                     c.sendall(header)
-        incoming: Dict[int, List[int]] = {}
-        srv.settimeout(60.0)
-        for _ in range(world - 1):
+        deadline = time.monotonic() + 60.0
+        while len(incoming) < world - 1:
+            left = deadline - time.monotonic()
+            if left <= 0:
+                raise RuntimeError(f"fd exchange: rank {rank} heard from {sorted(incoming)} only")
+            srv.settimeout(left)
             conn, _addr = srv.accept()
             with conn:
-                conn.settimeout(60.0)
-                msg, fds, _flags, _a = socket.recv_fds(conn, 8, 16)
-                sender, count = int(msg[:4]), int(msg[4:8])
-                if count != len(fds):
-                    raise RuntimeError(f"fd exchange: rank {sender} announced {count} descriptors, got {len(fds)}")
-                incoming[sender] = list(fds)
+                conn.settimeout(max(0.1, deadline - time.monotonic()))
+                fds: List[int] = []
+                try:
+                    cred = conn.getsockopt(socket.SOL_SOCKET, socket.SO_PEERCRED, struct.calcsize("3i"))
+                    pid, uid, _gid = struct.unpack("3i", cred)
+                    msg, fds, _flags, _a = socket.recv_fds(conn, 24, 16)
+                    fds = list(fds)
+                    sender, count = int(msg[16:20]), int(msg[20:24])    # ValueError on a garbled header
+                    good = (len(msg) == 24 and msg[:16] == token and 0 <= sender < world and sender != rank
+                            and sender not in incoming and uid == os.getuid() and pid == cards[sender][1]
+                            and count == len(fds))
+                except (ValueError, OSError, struct.error):
+                    good = False
+                if not good:
+                    for fd in fds:
+                        os.close(fd)
+                    continue                             # not one of ours: keep listening
+                incoming[sender] = fds
         group.dist.barrier(group=group.pg)
+        ok = True
         return incoming
     finally:
         srv.close()
+        if not ok:
+            for fds in incoming.values():
+                for fd in fds:
+                    try:
+                        os.close(fd)
+                    except OSError:
+                        pass
 
 
 class VmmBuffer:

@@ -49,8 +49,12 @@ def roberts_torch(img_u8: torch.Tensor) -> torch.Tensor:
 SHAPES = {
     "generic": [(1, 1), (3, 3), (5, 7), (33, 130), (257, 255)],
     "stream": [(1, 4), (2, 128), (64, 132), (300, 512), (1000, 1028), (9, 4096)],
-    "tma": [(1, 256), (33, 256), (300, 512), (1000, 1028), (2049, 2052), (31, 4096)],
-    "cluster": [(1, 256), (33, 256), (300, 512), (1000, 1028), (2049, 2052), (31, 4096), (70, 768)],
+    # widths with 0 < w % 256 <= 128 make the right-half warps skip the last tile column:
+    # with enough tile rows a CTA sees stored / skipped / stored (the staging-buffer case)
+    "tma": [(1, 256), (33, 256), (300, 512), (1000, 1028), (2049, 2052), (31, 4096), (9500, 384),
+            (4800, 1920)],
+    "cluster": [(1, 256), (33, 256), (300, 512), (1000, 1028), (2049, 2052), (31, 4096), (70, 768),
+                (9500, 384), (4800, 1920)],
 }
 
 

@@ -92,8 +92,23 @@ FD_WORKER = textwrap.dedent('''
             f.write(b"from %d to %d #%d" % (g.rank, dest, k)); f.flush(); f.seek(0)
             files.append(f); fds.append(f.fileno())
         out[dest] = fds
+    # a stray local process: right after the socket names went round, rank 0 also throws a
+    # message with a wrong token (and a descriptor) plus a garbled one at every listener
+    real_gather = dist.all_gather_object
+    def gather_then_intrude(cards, card, group=None):
+        real_gather(cards, card, group=group)
+        if g.rank == 0:
+            import socket
+            for name, _pid, _tok in cards:
+                for payload in (b"x" * 16 + b"   1   1", b"garbage"):
+                    with socket.socket(socket.AF_UNIX, socket.SOCK_STREAM) as c:
+                        c.connect(name)
+                        socket.send_fds(c, [payload], [files[0].fileno()])
+    dist.all_gather_object = gather_then_intrude
     got = exchange_fds(g, out)
+    dist.all_gather_object = real_gather
     assert sorted(got) == [r for r in range(g.world) if r != g.rank], got
+    assert all(len(v) == 2 for v in got.values()), got
     for sender, fds in got.items():
         for k, fd in enumerate(fds):
             with os.fdopen(fd, "rb") as f:

@@ -42,3 +42,18 @@ def test_png_conversion_matches_fixture(repo_root, tmp_path):
     png = ImgData(str(repo_root / "lab2/data/lenna.png"), out_dir=str(tmp_path), materialize=False)
     with open(repo_root / "lab2/test_data/lenna.data", "rb") as f:
         assert png.c_data_bytes == f.read()
+
+
+def test_lab3_sample_points_outside_the_image_are_an_error():
+    """A point outside the whole image would be skipped by every band's kernel and silently
+    drop out of the class statistics: pack_points refuses it on the host."""
+    import pytest
+    from cuda_mpi_openmp_b200.ops.classify import pack_points
+
+    ok = [np.array([[0, 0], [9, 4]]), np.array([[3, 2]])]
+    pts, off = pack_points(ok, w=10, h=5)
+    assert pts.tolist() == [0, 0, 9, 4, 3, 2] and off.tolist() == [0, 2, 3]
+    for bad in ([[10, 0]], [[0, 5]], [[-1, 2]], [[2, -1]]):
+        with pytest.raises(ValueError, match="outside"):
+            pack_points([np.array([[1, 1]]), np.array(bad)], w=10, h=5)
+    pack_points([np.array([[10, 0]])])          # no bounds given: packing only

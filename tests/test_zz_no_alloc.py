@@ -53,7 +53,7 @@ def _make(rng, n, key_type, device):
     return torch.from_numpy(k).to(device)
 
 
-@pytest.mark.parametrize("key_type", [KEY_I32, KEY_F32, KEY_U8])
+@pytest.mark.parametrize("key_type", [KEY_I32, KEY_F32, KEY_U8, KEY_U32])
 def test_two_calls_in_a_row_match_the_scratch_taking_entry_point(cuda_device, lib, key_type):
     sort_noalloc = _bind(lib)
     rng = np.random.default_rng(2024 + key_type)
@@ -63,6 +63,9 @@ def test_two_calls_in_a_row_match_the_scratch_taking_entry_point(cuda_device, li
     for n in (MAX_KEYS, 300_007):
         keys = _make(rng, n, key_type, cuda_device)
         want = _sort_with_caller_scratch(lib, keys, key_type)
+        if key_type == KEY_U32:                  # same bits, unsigned order: check the oracle too
+            assert np.array_equal(want.cpu().numpy().view(np.uint32),
+                                  np.sort(keys.cpu().numpy().view(np.uint32)))
         out = torch.empty_like(keys)
         torch.cuda.synchronize()
         free_before, _ = torch.cuda.mem_get_info(cuda_device)
@@ -79,6 +82,24 @@ def test_two_calls_in_a_row_match_the_scratch_taking_entry_point(cuda_device, li
     assert sort_noalloc(N.ptr(keys), N.ptr(keys), keys.numel(), key_type, stream) == 0
     torch.cuda.synchronize()
     assert torch.equal(keys.view(torch.uint8), want.view(torch.uint8))
+
+
+def test_buffers_that_are_only_four_byte_aligned(cuda_device, lib):
+    """A caller's buffers need not be 16-byte aligned (that only switches the vectorised
+    histogram loads off): input and output both start 4 bytes into an allocation."""
+    sort_noalloc = _bind(lib)
+    rng = np.random.default_rng(77)
+    n = 123_457
+    backing_in = _make(rng, n + 1, KEY_I32, cuda_device)
+    backing_out = torch.empty_like(backing_in)
+    keys, out = backing_in[1:], backing_out[1:]
+    assert keys.data_ptr() % 16 == 4 and out.data_ptr() % 16 == 4
+    want = _sort_with_caller_scratch(lib, keys, KEY_I32)
+    for _ in range(2):
+        out.zero_()
+        assert sort_noalloc(N.ptr(keys), N.ptr(out), n, KEY_I32, N.current_stream_ptr()) == 0
+        torch.cuda.synchronize()
+        assert torch.equal(out, want)
 
 
 def test_sizes_beyond_the_built_in_scratch_are_refused(cuda_device, lib):
