@@ -12,9 +12,12 @@ written) x pixels / device time, whole job, strong scaling (total work fixed).
 N > 1 is launched by the driver through torch.distributed.run (one rank per GPU); the
 ranks time the same K steps with CUDA events, the maximum over ranks is reported by
 rank 0 as ONE JSON line.  `e2e` is the same metric through the public pipeline API
-(`RobertsFilter.run_host`): every step copies the band from pinned host memory to the
-GPU, filters it and copies the result back.  `labs` carries the other labs' kernels
-at the same N (fewer steps) for BASELINE.md's table.
+(`ShardedRoberts.run_host`): every step copies the band from pinned host memory into
+the symmetric device band, filters it with the same fused kernel (halo row read from
+the neighbour GPU) and copies the result back.  `labs` carries the other labs' kernels
+at the same N (fewer steps) for BASELINE.md's table.  `verify` holds output checks run
+outside the timed regions (sampled blocks against the CPU oracles, sortedness and
+checksums, bit-identical class parameters); any false verdict makes the exit code 3.
 """
 from __future__ import annotations
 
@@ -100,7 +103,6 @@ def run_own(args):
     import torch
 
     from cuda_mpi_openmp_b200 import _native as N
-    from cuda_mpi_openmp_b200.models import RobertsFilter
     from cuda_mpi_openmp_b200.parallel import (ShardedClassifier, ShardedRoberts, ShardedSort, SoloPeerGroup,
                                                 init_distributed)
     from cuda_mpi_openmp_b200.utils import ClockSampler
@@ -137,6 +139,18 @@ def run_own(args):
     value = total_bytes / ms / 1e6
     peak, peak_kind = peak_gbs()
 
+    # ------------------------------------------------------------ verify the flagship output (untimed)
+    verify = {}
+    from cuda_mpi_openmp_b200.utils import verify as V
+    below_t = None
+    if world > 1 and rank < world - 1:                 # the neighbour's first row, read through the peer mapping
+        below_t = model.sym_in.peer_view(rank + 1, torch.int32, w).clone()
+    starts = V.sample_block_starts(model.h_local, w, n_blocks=16, rows=64, seed=rank)
+    v2 = V.roberts_blocks(model.band, model.out, below_t, starts, rows=64)
+    v2["byte_offsets_ge_2^32_sampled"] = bool(any(4 * w * y >= (1 << 32) for y in starts))
+    v2["ok"] = bool(group.all_reduce_max(0.0 if v2["ok"] else 1.0) == 0.0)
+    verify["lab2_blocks_vs_cpu_oracle"] = v2
+
     # ------------------------------------------------------------ end to end (host -> host)
     e2e = None
     if not args.no_e2e:
@@ -144,28 +158,24 @@ def run_own(args):
         host_in = torch.empty((model.h_local, w), dtype=torch.int32, pin_memory=True)
         host_out = torch.empty((model.h_local, w), dtype=torch.int32, pin_memory=True)
         host_in.copy_(model.band)                      # synthetic band, now resident in pinned host memory
-        below_host = None
-        if world > 1:                                  # halo row of the next band, exchanged once at set-up
-            import torch.distributed as dist
-            first = model.band[0].clone()
-            halo = torch.empty_like(first)
-            ops = []
-            if rank > 0:
-                ops.append(dist.P2POp(dist.isend, first, rank - 1))
-            if rank < world - 1:
-                ops.append(dist.P2POp(dist.irecv, halo, rank + 1))
-            for req in dist.batch_isend_irecv(ops):
-                req.wait()
-            if rank < world - 1:
-                below_host = halo.cpu().pin_memory()
-        pipe = RobertsFilter(dev, variant=args.variant)
-        e2e_ms = timed_steps(group, lambda: pipe.run_host(host_in, host_out, below_host), e2e_steps, 1)
-        check = bool(torch.equal(host_out[:64], model.out[:64].cpu()))
+        ref_out = model.out.clone()                    # device-path result of the same band
+        torch.cuda.synchronize()
+        group.barrier()
+        e2e_ms = timed_steps(group, lambda: model.run_host(host_in, host_out), e2e_steps, 1)
+        # the whole end-to-end output against the device-path output, compared on the device
+        same, piece = True, max(1, (1 << 30) // (4 * w))
+        for r0 in range(0, model.h_local, piece):
+            up = host_out[r0:r0 + piece].to(dev, non_blocking=True)
+            same = same and bool(torch.equal(up, ref_out[r0:r0 + piece]))
+        del ref_out
+        same = bool(group.all_reduce_max(0.0 if same else 1.0) == 0.0)
+        verify["lab2_e2e_equals_device_path"] = {"ok": same, "rows_compared": model.h_local * world}
         e2e = {"value": round(total_bytes / e2e_ms / 1e6, 2), "unit": "GB/s", "ms_per_step": round(e2e_ms, 3),
-               "steps": e2e_steps, "h2d_bytes_per_step": 4 * w * h + (world - 1) * 4 * w,
-               "d2h_bytes_per_step": 4 * w * h, "api": "RobertsFilter.run_host (pinned host -> GPU -> pinned host)",
-               "matches_device_path": check}
-        del host_in, host_out, pipe
+               "steps": e2e_steps, "h2d_bytes_per_step": 4 * w * h, "d2h_bytes_per_step": 4 * w * h,
+               "api": "ShardedRoberts.run_host (pinned host -> symmetric device band -> fused kernel with the "
+                      "peer-memory halo -> pinned host; chunked, three streams)",
+               "matches_device_path": same}
+        del host_in, host_out
     flag_out_sample = model.out[:2, :8].cpu().tolist()
     group.barrier()
     model.free()
@@ -208,6 +218,7 @@ def run_own(args):
                                               "stats": "in-kernel all-reduce" if args.exchange == "fused" else "nccl"}
         t = timed_steps(group, m3.fit, 20, 3)
         labs["lab3_stats_allreduce_32x4096pts"] = {"ms": round(t, 4)}
+        verify["lab3"] = verify_lab3(group, m3, classes, s3)
         if args.lab3_nvls and world > 1:
             try:
                 m3n = ShardedClassifier(group, s3, s3, classes, impl="nvls")
@@ -230,6 +241,7 @@ def run_own(args):
         err = group.ws_error() if world > 1 else 0
         labs["lab5_sort_2^31_int32"] = {"ms": round(t, 3), "Gkeys_per_s": round(n_total / t / 1e6, 2),
                                         "bucket_keys_rank0": m5.count(), "error_word": err}
+        verify["lab5"] = verify_lab5(group, m5, n_total)
         group.barrier()
         m5.free()
         del m5
@@ -253,7 +265,7 @@ def run_own(args):
                                 "slower than the 2+2 GiB copy MEASURED_PEAKS.json was taken on"},
             "clocks": {"sm_mhz": clock_summary["sm_mhz"], "sm_max_mhz": clock_summary["sm_max_mhz"],
                        "reasons": clock_summary["reasons"], "samples": clock_summary["samples"]},
-            "e2e": e2e, "gpu_launches": int(launches_timed), "labs": labs,
+            "e2e": e2e, "gpu_launches": int(launches_timed), "labs": labs, "verify": verify,
             "published_reference_note": "BASELINE.md has no published number for this config (reference numbers "
                                         "are A6000 launch-latency-bound <= 0.18 ms figures on <= 1 MP images)",
             "out_sample": flag_out_sample[0][:4],
@@ -263,6 +275,91 @@ def run_own(args):
         import torch.distributed as dist
         dist.barrier()
         dist.destroy_process_group()
+    if not all(v.get("ok", False) for v in verify.values()):
+        if rank == 0:
+            print(f"[bench] VERIFY FAILED: {json.dumps(verify)}", file=sys.stderr)
+        sys.exit(3)
+
+
+def verify_lab3(group, m3, classes, size):
+    """lab3 outside the timed region: (a) the all-reduced class parameters are bit-identical to
+    the CPU oracle's (exact integer moments of every band summed over the ranks, then the same
+    finalize arithmetic); (b) >= 1 M pixels of the classified image, sampled as whole rows from
+    every band, carry the class the CPU classifier assigns under those parameters."""
+    import numpy as np
+    import torch
+
+    from cuda_mpi_openmp_b200 import _native as N
+    from cuda_mpi_openmp_b200.models import MahalanobisClassifier
+    from cuda_mpi_openmp_b200.ops import classify as CL
+
+    world, rank = group.world, group.rank
+    m3.step()
+    torch.cuda.synchronize()
+    band = m3.band.cpu().numpy()                          # RGB untouched by classify, alpha = class
+    pts, off = CL.pack_points(classes, w=size, h=size)
+    mom = np.zeros((len(classes), CL.N_MOMENTS), dtype=np.int64)
+    N.lib().b200_cpu_lab3_moments(N.ptr(band), size, m3.y0, m3.h_local, N.ptr(pts), N.ptr(off), len(classes),
+                                  N.ptr(mom))
+    mom_t = torch.from_numpy(mom).to(group.device)
+    if world > 1:
+        group.dist.all_reduce(mom_t, op=group.dist.ReduceOp.SUM, group=group.pg)
+    mom = mom_t.cpu().numpy()
+    params = np.zeros((len(classes), CL.N_PARAMS), dtype=np.float64)
+    N.lib().b200_cpu_lab3_finalize(N.ptr(mom), len(classes), N.ptr(params))
+    got = m3.params.cpu().numpy()
+    params_ok = bool(np.array_equal(params.view(np.int64), got.view(np.int64)))
+    rows = max(8, (64 + world - 1) // world)              # >= 64 rows x 16384 px = 1 M pixels in total
+    ys = np.unique(np.concatenate([[0, m3.h_local - 1], np.random.default_rng(rank).integers(0, m3.h_local, rows)]))
+    sample = np.ascontiguousarray(band[ys]).view(np.uint8).reshape(len(ys), size, 4)
+    want = MahalanobisClassifier.reference_classify(sample, params)
+    bad = int((want[..., 3] != sample[..., 3]).sum())
+    ok = params_ok and bad == 0
+    ok = bool(group.all_reduce_max(0.0 if ok else 1.0) == 0.0)
+    return {"params_bit_identical_to_cpu_oracle": params_ok, "pixels_sampled": int(len(ys) * size * world),
+            "pixels_wrong": bad, "ok": ok}
+
+
+def verify_lab5(group, m5, n_total):
+    """lab5 outside the timed region: every rank's bucket is sorted, bucket r's last key is not
+    above bucket r+1's first key, the bucket sizes add up to n, and (sum, xor) of all keys is
+    the same before and after (nothing lost, nothing invented)."""
+    import torch
+
+    from cuda_mpi_openmp_b200.utils import verify as V
+
+    world = group.world
+    m5.step()
+    torch.cuda.synchronize()
+    res = m5.result()
+    cnt = int(res.numel())
+    sorted_ok = V.is_sorted(res)
+    s_in, x_in = V.checksum(m5.keys)
+    s_out, x_out = V.checksum(res)
+    first = int(res[0].item()) if cnt else 2 ** 31 - 1
+    last = int(res[-1].item()) if cnt else -2 ** 31
+    t = torch.tensor([cnt, s_in, s_out, x_in, x_out, first, last, int(sorted_ok)], dtype=torch.int64,
+                     device=group.device)
+    if world > 1:
+        allt = [torch.empty_like(t) for _ in range(world)]
+        group.dist.all_gather(allt, t, group=group.pg)
+    else:
+        allt = [t]
+    rows = [x.tolist() for x in allt]
+    total = sum(r[0] for r in rows)
+    sums_ok = sum(r[1] for r in rows) == sum(r[2] for r in rows)
+    xi = xo = 0
+    for r in rows:
+        xi ^= r[3]
+        xo ^= r[4]
+    nonempty = [r for r in rows if r[0] > 0]
+    bounds_ok = all(a[6] <= b[5] for a, b in zip(nonempty, nonempty[1:]))
+    all_sorted = all(r[7] == 1 for r in rows)
+    err = group.ws_error() if world > 1 else 0
+    ok = all_sorted and bounds_ok and total == n_total and sums_ok and xi == xo and err == 0
+    return {"buckets_sorted": all_sorted, "bucket_boundaries_ordered": bounds_ok, "keys_total": total,
+            "sum_checksum_equal": sums_ok, "xor_checksum_equal": xi == xo, "error_word": err,
+            "bucket_sizes": [r[0] for r in rows], "ok": ok}
 
 
 # ========================================================================= reference arm

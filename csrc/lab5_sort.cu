@@ -6,17 +6,25 @@
 //   1. one histogram kernel reads the keys once and builds all four digit
 //      histograms (privatised per warp in shared memory);
 //   2. per pass ONE kernel ranks and scatters: tiles of 8192 keys take a ticket,
-//      rank their keys inside each warp (lanes sharing a digit are found through a
-//      shared-memory OR word; MATCH.ANY is ADU-bound on B200 and ballots ALU-bound,
-//      see profiles/), publish the tile's digit counts and
+//      count their digits, publish the counts, rank their keys inside each warp
+//      (lanes sharing a digit are found through a shared-memory mask word;
+//      MATCH.ANY is ADU-bound on B200 and ballots ALU-bound, see profiles/),
 //      resolve their global offsets by decoupled look-back over earlier tiles
 //      (single 64-bit status|pass|value words, so no fences and one zero-fill
-//      serves all four passes), stage the keys in shared memory in digit order and
-//      write them out in coalesced runs.
+//      serves all four passes), and write the keys out in coalesced runs.
 // Traffic: 1 read + 4 x (read + write) of the keys = 9 x 4 B per key, plus
 // ~2 KB of look-back words per 32 KB tile.  uint8 keys are a counting sort
 // (histogram + fill).
+//
+// What bounds it (profiles/ncu_prof_lab5_v5a.md): the L1/shared-memory data pipe
+// moves ONE 128-byte wavefront per cycle per SM, and a warp access indexed by 32
+// random digits costs 3.5-5 wavefronts (bank conflicts).  A stable pass needs
+// five such accesses per 32 keys (count, mask OR, mask+position read, position
+// write, key placement), an unstable one two; with loads, stores and the per-tile
+// scan that is ~36 / ~24 wavefronts per 32 keys against 10.6 cycles per 32 keys of
+// HBM time.  DRAM sits at 20-30%; the kernels are shared-memory-bound, like CUB's.
 #include <cstdlib>
+#include <type_traits>
 
 #include "common.cuh"
 
@@ -28,22 +36,12 @@ constexpr int kRadix = 1 << kRadixBits;
 #define B200_SORT_THREADS 512
 #endif
 constexpr int kSortThreads = B200_SORT_THREADS;
-constexpr int kSortBlocksPerSm = 1024 / kSortThreads;
 constexpr int kSortWarps = kSortThreads / 32;
 constexpr int kItems = 16;
 constexpr int kTile = kSortThreads * kItems;  // 8192 keys
-#ifndef B200_SORT_PERSIST_DEFAULT
-#define B200_SORT_PERSIST_DEFAULT 0
-#endif
 #ifndef B200_SORT_LOOK
 #define B200_SORT_LOOK 8   /* 16 measured 6% slower */
 #endif
-#ifndef B200_SORT_BALLOT_ITEMS
-#define B200_SORT_BALLOT_ITEMS 0
-#endif
-// how many of a thread's 16 keys find their same-digit lanes with ballots; the rest
-// use shared-memory OR words (see sweep_tile)
-constexpr int kBallotItems = B200_SORT_BALLOT_ITEMS;
 
 // order-preserving bijection key bits -> unsigned
 template <int KT>
@@ -126,353 +124,9 @@ __device__ __forceinline__ void st_lookback(unsigned long long* p, unsigned long
   asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
 
-struct SweepSmem {
-  uint32_t keys[kTile];                   // 32 KB: keys in digit order
-  uint32_t warp_hist[kSortWarps][kRadix]; // 16 KB: per-warp digit counts -> offsets
-  unsigned long long global_off[kRadix];  // output index of (digit, tile-position 0)
-  uint32_t tile_start[kRadix];            // first tile position of each digit
-  uint32_t scan_tmp[kRadix / 32];
-  uint32_t tile_id;
-  uint32_t lane_bits[kSortWarps][kRadix]; // 16 KB: per-warp "which lanes hold digit d" words
-};
-
-// One tile of one pass.  FULL = the tile holds kTile real keys (every tile but the
-// last), which removes all the validity predicates from the hot loops.  To rank a
-// key a warp must find the lanes holding the same digit; the first NM of a thread's
-// kItems keys do it with ballots (ALU pipe, ~40 instructions), the rest through a
-// shared-memory OR word (LSU/shared-memory pipe), so that both pipes carry part of
-// the ranking work.  (MATCH.ANY, the obvious instruction, is ADU-bound on B200: one
-// warp per ~60 cycles per SM, measured — see profiles/ncu_prof_lab5.md.)
-struct NoHook {
-  __device__ __forceinline__ void operator()() const {}
-};
-
-// UNSTABLE: a keys-only LSD sort needs stability only to keep the order made by EARLIER
-// passes, so the first pass may place equal digits in any order.  It then ranks a key with
-// one shared-memory atomicAdd on a per-tile digit counter (rank inside the tile directly)
-// instead of finding its same-digit lanes: ~6 shared-memory operations per key become one.
-template <int KT, int NM, bool FULL, bool PREFETCHED = false, typename Hook = NoHook,
-          bool UNSTABLE = false>
-__device__ __forceinline__ void sweep_tile(SweepSmem& S, const uint32_t* __restrict__ in,
-                                           uint32_t* __restrict__ out, size_t tile_base,
-                                           uint32_t n_valid, uint32_t tile, int pass,
-                                           const unsigned long long* __restrict__ digit_base,
-                                           unsigned long long* __restrict__ lookback,
-                                           const uint32_t* staged = nullptr, Hook after_load = Hook(),
-                                           unsigned long long* __restrict__ group_lb = nullptr) {
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int shift = pass * kRadixBits;
-
-  // ---- load: warp-striped, logical order == memory order (keeps the pass stable).
-  // PREFETCHED: the tile was copied into shared memory (cp.async) while the previous
-  // tile was being processed; the caller re-arms that buffer after the first barrier.
-  uint32_t key[kItems];
-  const uint32_t w_off = warp * (kItems * 32) + lane;
-#pragma unroll
-  for (int i = 0; i < kItems; ++i) {
-    const uint32_t o = w_off + i * 32;
-    if (PREFETCHED)
-      key[i] = (FULL || o < n_valid) ? staged[o] : 0xffffffffu;
-    else
-      key[i] = (FULL || o < n_valid) ? ld_stream_u32(in + tile_base + o) : 0xffffffffu;
-  }
-
-  // ---- rank inside the warp: find the lanes with my digit; the highest of them
-  // bumps the warp's counter for that digit and broadcasts the old value
-  uint32_t dr[kItems];  // digit << 16 | rank inside (warp, digit)
-  uint32_t* wh = S.warp_hist[warp];
-  uint32_t* lb = S.lane_bits[warp];
-  const uint32_t le_mask = 0xffffffffu >> (31 - lane);
-  if (UNSTABLE) {
-    // warp_hist[0][] doubles as the per-tile digit counter (zeroed by the kernel prologue)
-#pragma unroll
-    for (int i = 0; i < kItems; ++i) {
-      const uint32_t d = (to_ordered<KT>(key[i]) >> shift) & 0xff;
-      if (FULL || (w_off + i * 32) < n_valid)
-        dr[i] = (d << 16) | atomicAdd(&S.warp_hist[0][d], 1u);  // rank < kTile = 2^13
-      else
-        dr[i] = 0xffffffffu;  // padding: not counted, not staged
-    }
-  } else {
-#pragma unroll
-    for (int i = 0; i < kItems; ++i) {
-      // padding keys rank as digit 255 *after* every real key (they come last)
-      uint32_t d = (to_ordered<KT>(key[i]) >> shift) & 0xff;
-      if (!FULL && (w_off + i * 32) >= n_valid) d = 0xffu;
-      uint32_t peers;
-      const bool via_smem = i >= NM;  // compile-time after unrolling
-      if (via_smem) {
-        // match through shared memory: every lane ORs its bit into the word of its
-        // digit, then reads the word back — three LSU operations instead of 40 ALU ones
-        atomicOr(&lb[d], 1u << lane);
-        __syncwarp();
-        peers = lb[d];
-        __syncwarp();
-      } else {
-        peers = match_any_bits<kRadixBits>(d);
-      }
-      const int leader = 31 - __clz(peers);
-      const uint32_t below_incl = __popc(peers & le_mask);  // on the leader: the group size
-      uint32_t old = 0;
-      if (lane == leader) {
-        old = wh[d];
-        wh[d] = old + below_incl;
-        if (via_smem) lb[d] = 0;  // leave the word clean for the next key
-      }
-      old = __shfl_sync(0xffffffffu, old, leader);
-      dr[i] = (d << 16) | (old + below_incl - 1);
-      __syncwarp();
-    }
-}
-  __syncthreads();
-  after_load();  // every thread holds its keys in registers: the staging buffer is free
-
-  // ---- per digit: scan over warps, publish the tile aggregate, digit scan
-  uint32_t count = 0, real = 0, start = 0;
-  const unsigned long long tag = ((unsigned long long)pass << kPassShift);
-  if (tid < kRadix) {
-    if (UNSTABLE) {
-      count = S.warp_hist[0][tid];  // padding keys were never counted
-    } else {
-#pragma unroll
-      for (int wv = 0; wv < kSortWarps; ++wv) count += S.warp_hist[wv][tid];
-    }
-    real = count;
-    if (!UNSTABLE && !FULL && tid == kRadix - 1) real -= (kTile - n_valid);  // drop the padding keys
-    st_lookback(lookback + (size_t)tile * kRadix + tid, (kStAggregate << kStatusShift) | tag | real);
-
-    // exclusive scan of `count` over the 256 digits -> tile_start
-    uint32_t inc = count;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
-      if (lane >= o) inc += t;
-    }
-    if (lane == 31) S.scan_tmp[warp] = inc;
-    asm volatile("bar.sync 1, 256;" ::: "memory");  // the kRadix digit threads only
-    uint32_t base = 0;
-    for (int wv = 0; wv < warp; ++wv) base += S.scan_tmp[wv];
-    start = base + inc - count;
-    S.tile_start[tid] = start;
-    // warp_hist[w][d] := tile position of the first key of (warp w, digit d)
-    if (!UNSTABLE) {
-      uint32_t run = start;
-#pragma unroll
-      for (int wv = 0; wv < kSortWarps; ++wv) {
-        const uint32_t c = S.warp_hist[wv][tid];
-        S.warp_hist[wv][tid] = run;
-        run += c;
-      }
-    }
-  }
-  __syncthreads();
-
-  // ---- stage keys in digit order (needs only tile-local offsets; doing it before
-  // the look-back frees the key registers for the probes below)
-#pragma unroll
-  for (int i = 0; i < kItems; ++i) {
-    const uint32_t d = dr[i] >> 16;
-    if (UNSTABLE) {
-      if (FULL || dr[i] != 0xffffffffu) S.keys[S.tile_start[d] + (dr[i] & 0xffffu)] = key[i];
-    } else {
-      S.keys[S.warp_hist[warp][d] + (dr[i] & 0xffffu)] = key[i];
-    }
-  }
-
-  if (tid < kRadix) {
-    // decoupled look-back: sum aggregates of earlier tiles until an inclusive one.
-    // kLook predecessors are probed per round with independent loads (one L2 round
-    // trip instead of kLook).  With ~300 tiles in flight the walk back to the last
-    // finished tile was ~95 entries = 12 dependent L2 round trips per tile (a third of
-    // all warp time, profiles/ncu_prof_lab5_v3.md), so the walk is two-level: entries
-    // of my own group of kGroupTiles tiles first, then one entry per earlier GROUP (the
-    // last tile of a group publishes the group's aggregate, later its inclusive sum).
-    unsigned long long excl = 0;
-    constexpr int kLook = B200_SORT_LOOK;
-    // walks arr[from], arr[from-1], ... arr[lo]; true when it ended on an inclusive entry
-    auto walk = [&](const unsigned long long* arr, int64_t from, int64_t lo) -> bool {
-      bool inclusive = false;
-      for (int64_t t = from; t >= lo;) {
-        unsigned long long e[kLook];
-#pragma unroll
-        for (int j = 0; j < kLook; ++j)
-          e[j] = (t - j >= lo) ? ld_lookback(arr + (size_t)(t - j) * kRadix + tid) : 0ull;
-        bool done = false;
-#pragma unroll
-        for (int j = 0; j < kLook; ++j) {
-          if (done || t < lo) continue;
-          const unsigned long long st = e[j] >> kStatusShift;
-          if (st == 0 || ((e[j] >> kPassShift) & 0xf) != (unsigned long long)pass) {
-            done = true;  // not published yet: probe again from this entry
-            continue;
-          }
-          excl += e[j] & kValueMask;
-          --t;
-          if (st == kStInclusive) {
-            inclusive = true;
-            t = lo - 1;
-            done = true;
-          }
-        }
-      }
-      return inclusive;
-    };
-    if (group_lb == nullptr) {
-      walk(lookback, (int64_t)tile - 1, 0);
-    } else {
-      const int64_t grp = tile / kGroupTiles, grp_begin = grp * kGroupTiles;
-      const bool group_end = (tile % kGroupTiles) == kGroupTiles - 1;
-      if (!walk(lookback, (int64_t)tile - 1, grp_begin)) {
-        // excl = sum of my group's earlier aggregates
-        if (group_end)
-          st_lookback(group_lb + (size_t)grp * kRadix + tid,
-                      (kStAggregate << kStatusShift) | tag | (excl + real));
-        walk(group_lb, grp - 1, 0);
-      }
-      if (group_end)
-        st_lookback(group_lb + (size_t)grp * kRadix + tid,
-                    (kStInclusive << kStatusShift) | tag | (excl + real));
-    }
-    st_lookback(lookback + (size_t)tile * kRadix + tid,
-                (kStInclusive << kStatusShift) | tag | (excl + real));
-    S.global_off[tid] = digit_base[tid] + excl - start;
-  }
-  __syncthreads();
-
-  // ---- coalesced runs out
-#pragma unroll
-  for (int i = 0; i < kItems; ++i) {
-    const uint32_t p = tid + i * kSortThreads;
-    if (FULL || p < n_valid) {
-      const uint32_t k = S.keys[p];
-      const uint32_t d = (to_ordered<KT>(k) >> shift) & 0xff;
-      out[S.global_off[d] + p] = k;
-    }
-  }
-}
-
-template <int KT, int NM>
-__global__ void __launch_bounds__(kSortThreads, kSortBlocksPerSm)
-    sort_onesweep_kernel(const uint32_t* __restrict__ in, uint32_t* __restrict__ out, size_t n,
-                         const unsigned long long* __restrict__ n_dev, int pass,
-                         const unsigned long long* __restrict__ digit_base /*[256]*/,
-                         unsigned long long* __restrict__ lookback /*[tiles][256]*/,
-                         uint32_t* __restrict__ ticket) {
-  extern __shared__ __align__(16) uint8_t smem_raw[];
-  SweepSmem& S = *reinterpret_cast<SweepSmem*>(smem_raw);
-  const int tid = threadIdx.x;
-  if (tid == 0) S.tile_id = atomicAdd(ticket, 1u);
-  for (int i = tid; i < kSortWarps * kRadix; i += kSortThreads) {
-    (&S.warp_hist[0][0])[i] = 0;
-    if (NM < kItems) (&S.lane_bits[0][0])[i] = 0;
-  }
-  __syncthreads();
-  const uint32_t tile = S.tile_id;
-  const size_t tile_base = (size_t)tile * kTile;
-  // the grid is one CTA per tile of the capacity; the group entries follow the tile entries
-  unsigned long long* group_lb = lookback + (size_t)gridDim.x * kRadix;
-  if (n_dev) n = (size_t)*n_dev;
-  if (tile_base >= n) return;  // grid was sized for the capacity, not the actual length
-  const uint32_t n_valid = (uint32_t)min((size_t)kTile, n - tile_base);
-  if (pass < 0) {  // first pass, flagged by the host as ~pass: may be unstable
-    pass = ~pass;
-    if (n_valid == kTile)
-      sweep_tile<KT, NM, true, false, NoHook, true>(S, in, out, tile_base, n_valid, tile, pass,
-                                                    digit_base, lookback, nullptr, NoHook(), group_lb);
-    else
-      sweep_tile<KT, NM, false, false, NoHook, true>(S, in, out, tile_base, n_valid, tile, pass,
-                                                     digit_base, lookback, nullptr, NoHook(), group_lb);
-    return;
-  }
-  if (n_valid == kTile)
-    sweep_tile<KT, NM, true>(S, in, out, tile_base, n_valid, tile, pass, digit_base, lookback, nullptr,
-                             NoHook(), group_lb);
-  else
-    sweep_tile<KT, NM, false>(S, in, out, tile_base, n_valid, tile, pass, digit_base, lookback, nullptr,
-                              NoHook(), group_lb);
-}
-
-// Persistent variant: two CTAs per SM stay resident and pull tiles by ticket; the
-// NEXT tile's keys (and its ticket) are fetched with cp.async while the current
-// tile is ranked and scattered, which takes the ticket round trip and the DRAM
-// latency of the key load off the critical path of every tile.
-struct SweepSmemPersistent {
-  SweepSmem base;
-  alignas(16) uint32_t staged[kTile];  // 32 KB: the next tile, landed by cp.async (16-byte chunks)
-  uint32_t next_tile;
-};
-
-__device__ __forceinline__ void cp_async_16(void* smem_dst, const void* gmem_src, uint32_t src_bytes) {
-  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(smem_u32(smem_dst)),
-               "l"(gmem_src), "r"(src_bytes)
-               : "memory");
-}
-__device__ __forceinline__ void cp_async_wait_all() {
-  asm volatile("cp.async.wait_all;" ::: "memory");
-}
-
-template <int KT, int NM>
-__global__ void __launch_bounds__(kSortThreads, kSortBlocksPerSm)
-    sort_onesweep_persistent_kernel(const uint32_t* __restrict__ in, uint32_t* __restrict__ out,
-                                    size_t n, const unsigned long long* __restrict__ n_dev, int pass,
-                                    const unsigned long long* __restrict__ digit_base,
-                                    unsigned long long* __restrict__ lookback,
-                                    uint32_t* __restrict__ ticket) {
-  extern __shared__ __align__(16) uint8_t smem_raw[];
-  SweepSmemPersistent& PS = *reinterpret_cast<SweepSmemPersistent*>(smem_raw);
-  SweepSmem& S = PS.base;
-  const int tid = threadIdx.x;
-  if (n_dev) n = (size_t)*n_dev;
-  const size_t n_tiles = (n + kTile - 1) / kTile;
-
-  auto prefetch = [&](uint32_t t) {  // copy tile t into PS.staged (zero-fills past n)
-    if (t >= n_tiles) return;
-    const size_t base = (size_t)t * kTile;
-    const size_t left = n - base;  // keys available from `base`
-#pragma unroll
-    for (int j = 0; j < kTile / 4 / kSortThreads; ++j) {
-      const uint32_t c = tid + j * kSortThreads;  // 16-byte chunk of the tile
-      const size_t first = (size_t)c * 4;
-      const uint32_t bytes = first >= left ? 0u : (uint32_t)min((size_t)16, (left - first) * 4);
-      cp_async_16(&PS.staged[c * 4], in + base + first, bytes);
-    }
-  };
-
-  if (tid == 0) PS.next_tile = atomicAdd(ticket, 1u);
-  __syncthreads();
-  uint32_t tile = PS.next_tile;
-  prefetch(tile);
-  while (tile < n_tiles) {
-    for (int i = tid; i < kSortWarps * kRadix; i += kSortThreads) {
-      (&S.warp_hist[0][0])[i] = 0;
-      if (NM < kItems) (&S.lane_bits[0][0])[i] = 0;
-    }
-    cp_async_wait_all();
-    __syncthreads();  // staged keys + zeroed counters visible; previous tile fully written out
-    if (tid == 0) PS.next_tile = atomicAdd(ticket, 1u);  // resolved long before it is read
-    uint32_t next = 0;
-    auto rearm = [&]() {  // runs after sweep_tile's first barrier: keys are in registers
-      next = PS.next_tile;
-      prefetch(next);
-    };
-    const size_t tile_base = (size_t)tile * kTile;
-    const uint32_t n_valid = (uint32_t)min((size_t)kTile, n - tile_base);
-    if (n_valid == kTile)
-      sweep_tile<KT, NM, true, true>(S, in, out, tile_base, n_valid, tile, pass, digit_base, lookback,
-                                     PS.staged, rearm);
-    else
-      sweep_tile<KT, NM, false, true>(S, in, out, tile_base, n_valid, tile, pass, digit_base,
-                                      lookback, PS.staged, rearm);
-    tile = next;
-  }
-}
-
-// ------------------------------------------------------------------ pass kernel, second generation
-// What the profile of the kernel above said (profiles/ncu_prof_lab5_v4.md): 60 warp
-// instructions per 32 keys, issue slots 44% busy, 5.8 warps per issue parked on a CTA
-// barrier, two CTAs per SM.  This kernel does the same job (one ticketed tile, look-back,
-// coalesced runs out) with
-//   * an EARLY COUNT: every key first bumps its (warp, digit) counter, so the tile's digit
+// ------------------------------------------------------------------ onesweep pass
+// One ticketed tile per CTA:
+//   * EARLY COUNT: every key first bumps its (warp, digit) counter, so the tile's digit
 //     counts exist before any ranking; the digit threads turn them into tile positions and
 //     publish the tile aggregate right away (successor tiles never wait for our ranking);
 //   * ranking that writes each key straight to its tile position (no rank registers, no
@@ -480,14 +134,24 @@ __global__ void __launch_bounds__(kSortThreads, kSortBlocksPerSm)
 //     shared word per (warp, digit) - low half = lane mask of the current row (atomicOr),
 //     high half = next free tile position - read with one LDS.64 and rewritten by the
 //     group's highest lane with one STS.64 (which also clears the mask for the next row);
+//   * the FIRST pass has no earlier order to keep: it counts on CTA-wide counters, turns
+//     them into cursors and places every key with one atomicAdd on its digit's cursor;
 //   * keys kept in their ordered (unsigned-comparable) form between passes: the first
 //     pass converts on load, the last one converts back on store, the two in the middle
 //     extract a digit with a single byte-permute;
-//   * 40 registers, three CTAs (48 warps) per SM.
-struct PassSmem {
+//   * 40 registers, no spills, three CTAs (48 warps) per SM.
+// Tried on this kernel and dropped (B200, 2^26 uniform keys, device ms for the whole sort):
+// 8 or 16 of a thread's 16 rows matched with ballots instead of the mask word 1.38 / 1.42
+// against 1.33 (the ALU pipe fills up as the L1 pipe empties); two CTAs per SM at 64
+// registers 1.48; the first-generation kernel (ranks kept in registers, keys staged in a
+// second loop, per-pass to_ordered) 1.43.
+// WIDE: the array has 2^32 keys or more, so output indices need 64 bits
+template <bool WIDE>
+struct PassSmemT {
+  using Index = typename std::conditional<WIDE, unsigned long long, uint32_t>::type;
   uint32_t keys[kTile];                         // 32 KB: keys in digit order
   unsigned long long pair[kSortWarps][kRadix];  // 32 KB: {lane mask of the row, next tile position}
-  unsigned long long global_off[kRadix];        // byte address in `out` of (digit, tile position 0)
+  Index global_off[kRadix];                     // index in `out` of (digit, tile position 0), modulo 2^bits
   uint32_t scan_tmp[kRadix / 32];
   uint32_t tile_id;
 };
@@ -504,6 +168,30 @@ __device__ __forceinline__ uint2 lds_pair(const unsigned long long* p) {
 __device__ __forceinline__ void sts_pair(unsigned long long* p, uint32_t lo, uint32_t hi) {
   asm volatile("st.volatile.shared.v2.u32 [%0], {%1, %2};" ::"r"(smem_u32(p)), "r"(lo), "r"(hi) : "memory");
 }
+// counter[digit(key)] += 1 with the digit and the address formed inside one statement, so the
+// compiler cannot hoist sixteen addresses above the loop (it spilled the KEYS to do that)
+template <int STRIDE>  // bytes per table entry; the counter is the entry's LAST 32-bit word
+__device__ __forceinline__ void count_digit(uint32_t key, uint32_t sel, uint32_t table_smem) {
+  asm volatile(
+      "{\n\t.reg .b32 d, a;\n\t"
+      "prmt.b32 d, %0, 0, %1;\n\t"
+      "mad.lo.u32 a, d, %3, %2;\n\t"
+      "red.shared.add.u32 [a+%4], 1;\n\t}" ::"r"(key), "r"(sel), "r"(table_smem), "n"(STRIDE), "n"(STRIDE - 4)
+      : "memory");
+}
+// position = cursor[digit(key)]++ on a table of 4-byte entries
+__device__ __forceinline__ uint32_t take_slot(uint32_t key, uint32_t sel, uint32_t table_smem) {
+  uint32_t r;
+  asm volatile(
+      "{\n\t.reg .b32 d, a;\n\t"
+      "prmt.b32 d, %1, 0, %2;\n\t"
+      "mad.lo.u32 a, d, 4, %3;\n\t"
+      "atom.shared.add.u32 %0, [a], 1;\n\t}"
+      : "=r"(r)
+      : "r"(key), "r"(sel), "r"(table_smem)
+      : "memory");
+  return r;
+}
 
 template <int KT>
 __device__ __forceinline__ uint32_t from_ordered(uint32_t o) {
@@ -512,8 +200,8 @@ __device__ __forceinline__ uint32_t from_ordered(uint32_t o) {
   return o;
 }
 
-template <int KT, bool FIRST, bool LAST, bool FULL>
-__device__ __forceinline__ void pass_tile(PassSmem& S, const uint32_t* __restrict__ in,
+template <int KT, bool FIRST, bool LAST, bool FULL, bool WIDE>
+__device__ __forceinline__ void pass_tile(PassSmemT<WIDE>& S, const uint32_t* __restrict__ in,
                                           uint32_t* __restrict__ out, size_t tile_base,
                                           uint32_t n_valid, uint32_t tile, int pass,
                                           const unsigned long long* __restrict__ digit_base,
@@ -523,11 +211,11 @@ __device__ __forceinline__ void pass_tile(PassSmem& S, const uint32_t* __restric
   const uint32_t sel = 0x4440u | (uint32_t)pass;  // byte `pass` of the key -> bits 0..7
   const uint32_t w_off = warp * (kItems * 32) + lane;
   unsigned long long* pr = S.pair[warp];
-  uint32_t* pr_hi = reinterpret_cast<uint32_t*>(pr) + 1;  // high words, stride 2
+  // first pass: one counter per digit for the whole CTA (S.pair[0] reused as 256 words)
+  uint32_t* cta_cnt = reinterpret_cast<uint32_t*>(&S.pair[0][0]);
 
   // ---- load (warp-striped: logical order == memory order) + early count
   uint32_t key[kItems];
-  uint32_t rk[FIRST ? kItems : 1];
 #pragma unroll
   for (int i = 0; i < kItems; ++i) {
     const uint32_t o = w_off + i * 32;
@@ -535,15 +223,13 @@ __device__ __forceinline__ void pass_tile(PassSmem& S, const uint32_t* __restric
     if (FIRST) k = to_ordered<KT>(k);
     key[i] = k;
   }
+  const uint32_t tbl = FIRST ? smem_u32(cta_cnt) : smem_u32(pr);
 #pragma unroll
-  for (int i = 0; i < kItems; ++i) {
-    const uint32_t d = __byte_perm(key[i], 0, sel);
+  for (int i = 0; i < kItems; ++i)
     if (FULL || (w_off + i * 32) < n_valid) {
-      // the first pass has no earlier order to keep: the counter's old value IS the rank
-      if (FIRST) rk[i] = atomicAdd(&pr_hi[2 * d], 1u);
-      else atomicAdd(&pr_hi[2 * d], 1u);
+      if (FIRST) count_digit<4>(key[i], sel, tbl);
+      else count_digit<8>(key[i], sel, tbl);
     }
-  }
   __syncthreads();
 
   // ---- digit threads: counts -> tile positions, publish the aggregate, scan the digits
@@ -551,8 +237,12 @@ __device__ __forceinline__ void pass_tile(PassSmem& S, const uint32_t* __restric
   const unsigned long long tag = ((unsigned long long)pass << kPassShift);
   if (tid < kRadix) {
     uint32_t* col = reinterpret_cast<uint32_t*>(&S.pair[0][tid]) + 1;
+    if (FIRST) {
+      count = cta_cnt[tid];
+    } else {
 #pragma unroll
-    for (int wv = 0; wv < kSortWarps; ++wv) count += col[wv * kRadix * 2];
+      for (int wv = 0; wv < kSortWarps; ++wv) count += col[wv * kRadix * 2];
+    }
     st_lookback(lookback + (size_t)tile * kRadix + tid, (kStAggregate << kStatusShift) | tag | count);
     uint32_t inc = count;
 #pragma unroll
@@ -565,23 +255,26 @@ __device__ __forceinline__ void pass_tile(PassSmem& S, const uint32_t* __restric
     uint32_t base = 0;
     for (int wv = 0; wv < warp; ++wv) base += S.scan_tmp[wv];
     start = base + inc - count;
-    uint32_t run = start;
+    if (FIRST) {
+      cta_cnt[tid] = start;  // from count to cursor: the next free tile position of the digit
+    } else {
+      uint32_t run = start;
 #pragma unroll
-    for (int wv = 0; wv < kSortWarps; ++wv) {
-      const uint32_t c = col[wv * kRadix * 2];
-      col[wv * kRadix * 2] = run;  // first tile position of (warp wv, digit tid)
-      run += c;
+      for (int wv = 0; wv < kSortWarps; ++wv) {
+        const uint32_t c = col[wv * kRadix * 2];
+        col[wv * kRadix * 2] = run;  // first tile position of (warp wv, digit tid)
+        run += c;
+      }
     }
   }
   __syncthreads();
 
   // ---- rank + place
   if (FIRST) {
+    // no earlier order to keep: a key takes the next free position of its digit
 #pragma unroll
-    for (int i = 0; i < kItems; ++i) {
-      const uint32_t d = __byte_perm(key[i], 0, sel);
-      if (FULL || (w_off + i * 32) < n_valid) S.keys[pr_hi[2 * d] + rk[i]] = key[i];
-    }
+    for (int i = 0; i < kItems; ++i)
+      if (FULL || (w_off + i * 32) < n_valid) S.keys[take_slot(key[i], sel, tbl)] = key[i];
   } else {
     const uint32_t lane_bit = 1u << lane;
     const uint32_t le_mask = 0xffffffffu >> (31 - lane);
@@ -594,10 +287,11 @@ __device__ __forceinline__ void pass_tile(PassSmem& S, const uint32_t* __restric
       uint2 v = make_uint2(0u, 0u);  // {lanes of this row with my digit, next free position}
       if (valid) v = lds_pair(&pr[d]);
       __syncwarp();
+      const uint32_t peers = v.x, pos = v.y;
       // on the group's highest lane `next` is the position after the whole group
-      const uint32_t next = v.y + __popc(v.x & le_mask);
+      const uint32_t next = pos + __popc(peers & le_mask);
       if (valid) {
-        if ((v.x >> lane) == 1u) sts_pair(&pr[d], 0u, next);
+        if ((peers >> lane) == 1u) sts_pair(&pr[d], 0u, next);
         S.keys[next - 1] = key[i];
       }
       __syncwarp();
@@ -648,8 +342,10 @@ __device__ __forceinline__ void pass_tile(PassSmem& S, const uint32_t* __restric
                   (kStInclusive << kStatusShift) | tag | (excl + count));
     st_lookback(lookback + (size_t)tile * kRadix + tid,
                 (kStInclusive << kStatusShift) | tag | (excl + count));
-    S.global_off[tid] =
-        (unsigned long long)(uintptr_t)out + 4ull * (digit_base[tid] + excl - start);
+    // modular index arithmetic (32 bits unless WIDE): (index of the digit's first key) -
+    // (its tile position) may wrap below zero, the sum in the output loop wraps back
+    using Index = typename PassSmemT<WIDE>::Index;
+    S.global_off[tid] = (Index)(digit_base[tid] + excl) - (Index)start;
   }
   __syncthreads();
 
@@ -660,24 +356,25 @@ __device__ __forceinline__ void pass_tile(PassSmem& S, const uint32_t* __restric
     if (FULL || p < n_valid) {
       const uint32_t k = S.keys[p];
       const uint32_t d = __byte_perm(k, 0, sel);
-      uint32_t* dst = reinterpret_cast<uint32_t*>((uintptr_t)(S.global_off[d] + 4ull * p));
-      *dst = LAST ? from_ordered<KT>(k) : k;
+      out[(typename PassSmemT<WIDE>::Index)(S.global_off[d] + p)] = LAST ? from_ordered<KT>(k) : k;
     }
   }
 }
 
-template <int KT, bool FIRST, bool LAST, int BLOCKS = B200_SORT_PASS_BLOCKS>
-__global__ void __launch_bounds__(kSortThreads, BLOCKS)
+template <int KT, bool FIRST, bool LAST, bool WIDE>
+__global__ void __launch_bounds__(kSortThreads, B200_SORT_PASS_BLOCKS)
     sort_pass_kernel(const uint32_t* __restrict__ in, uint32_t* __restrict__ out, size_t n,
                      const unsigned long long* __restrict__ n_dev, int pass,
                      const unsigned long long* __restrict__ digit_base /*[256]*/,
                      unsigned long long* __restrict__ lookback /*[tiles][256] then [groups][256]*/,
                      uint32_t* __restrict__ ticket) {
   extern __shared__ __align__(16) uint8_t smem_raw[];
-  PassSmem& S = *reinterpret_cast<PassSmem*>(smem_raw);
+  PassSmemT<WIDE>& S = *reinterpret_cast<PassSmemT<WIDE>*>(smem_raw);
   const int tid = threadIdx.x;
   if (tid == 0) S.tile_id = atomicAdd(ticket, 1u);
-  {  // each warp clears its own 2 KB of counter words
+  if (FIRST) {  // only the CTA-wide digit counters are used
+    if (tid < kRadix) reinterpret_cast<uint32_t*>(&S.pair[0][0])[tid] = 0;
+  } else {  // each warp clears its own 2 KB of counter words
     uint4* z = reinterpret_cast<uint4*>(S.pair[tid >> 5]);
 #pragma unroll
     for (int j = 0; j < kRadix * 8 / 16 / 32; ++j) z[(tid & 31) + 32 * j] = make_uint4(0, 0, 0, 0);
@@ -690,11 +387,11 @@ __global__ void __launch_bounds__(kSortThreads, BLOCKS)
   if (tile_base >= n) return;  // grid was sized for the capacity, not the actual length
   const uint32_t n_valid = (uint32_t)min((size_t)kTile, n - tile_base);
   if (n_valid == kTile)
-    pass_tile<KT, FIRST, LAST, true>(S, in, out, tile_base, n_valid, tile, pass, digit_base, lookback,
-                                     group_lb);
+    pass_tile<KT, FIRST, LAST, true, WIDE>(S, in, out, tile_base, n_valid, tile, pass, digit_base, lookback,
+                                         group_lb);
   else
-    pass_tile<KT, FIRST, LAST, false>(S, in, out, tile_base, n_valid, tile, pass, digit_base,
-                                      lookback, group_lb);
+    pass_tile<KT, FIRST, LAST, false, WIDE>(S, in, out, tile_base, n_valid, tile, pass, digit_base,
+                                          lookback, group_lb);
 }
 
 // ------------------------------------------------------------------ uint8 keys
@@ -771,60 +468,44 @@ static SortScratch carve(void* scratch, size_t n) {
   return s;
 }
 
+using PassKernel = void (*)(const uint32_t*, uint32_t*, size_t, const unsigned long long*, int,
+                            const unsigned long long*, unsigned long long*, uint32_t*);
+
+template <int KT, bool WIDE>
+static int sort32_passes(const uint32_t* input, uint32_t* keys, uint32_t* tmp, size_t n,
+                         const unsigned long long* n_dev, const SortScratch& sc, cudaStream_t st) {
+  const PassKernel pass_first = sort_pass_kernel<KT, true, false, WIDE>;
+  const PassKernel pass_mid = sort_pass_kernel<KT, false, false, WIDE>;
+  const PassKernel pass_last = sort_pass_kernel<KT, false, true, WIDE>;
+  constexpr int smem = (int)sizeof(PassSmemT<WIDE>);
+  static PerDeviceOnce attr_once;  // one per (key type, index width): the kernels differ
+  if (int rc = attr_once.run("sort", [&]() -> int {
+        for (PassKernel k : {pass_first, pass_mid, pass_last}) {
+          B200_CUDA_OK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+          B200_CUDA_OK(cudaFuncSetAttribute(k, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+        }
+        return 0;
+      }))
+    return rc;
+  // pass 0 reads the caller's input (which may be a separate, untouched buffer),
+  // then the passes ping-pong tmp <-> keys and the fourth one lands in `keys`
+  const uint32_t* src = input;
+  uint32_t* dst = tmp;
+  for (int pass = 0; pass < 4; ++pass) {
+    const PassKernel k = pass == 0 ? pass_first : pass == 3 ? pass_last : pass_mid;
+    k<<<(unsigned)sc.tiles, kSortThreads, smem, st>>>(src, dst, n, n_dev, pass, sc.hist + pass * kRadix,
+                                                     sc.lookback, sc.tickets + pass);
+    B200_LAUNCH_OK();
+    src = dst;
+    dst = (dst == tmp) ? keys : tmp;
+  }
+  return 0;  // four passes: the result is in `keys`
+}
+
 template <int KT>
 static int sort32(const uint32_t* input, uint32_t* keys, uint32_t* tmp, size_t n,
                   const unsigned long long* n_dev, const SortScratch& sc, cudaStream_t st) {
   const int sms = device_info().sm_count;
-  // how many of the 16 keys per thread are matched with ballots (the rest go through
-  // shared memory); tunable: B200LABS_SORT_BALLOT=0|8|16
-  static const int nm = [] {
-    const char* e = getenv("B200LABS_SORT_BALLOT");
-    int v = e ? atoi(e) : kBallotItems;
-    return v <= 0 ? 0 : v <= 8 ? 8 : 16;
-  }();
-  using Kernel = void (*)(const uint32_t*, uint32_t*, size_t, const unsigned long long*, int,
-                          const unsigned long long*, unsigned long long*, uint32_t*);
-  const Kernel kernel = nm == 0   ? sort_onesweep_kernel<KT, 0>
-                        : nm == 8 ? sort_onesweep_kernel<KT, 8>
-                                  : sort_onesweep_kernel<KT, 16>;
-  // persistent CTAs with cp.async prefetch of the next tile (B200LABS_SORT_PERSIST=0 disables)
-  static const bool persist_env = [] {
-    const char* e = getenv("B200LABS_SORT_PERSIST");
-    return e ? atoi(e) != 0 : (B200_SORT_PERSIST_DEFAULT != 0);
-  }();
-  static const bool unstable_first = [] {
-    const char* e = getenv("B200LABS_SORT_UNSTABLE_FIRST");
-    return e ? atoi(e) != 0 : true;
-  }();
-  const bool persist = persist_env && nm == 0 && ((((uintptr_t)input) | ((uintptr_t)keys) | ((uintptr_t)tmp)) & 15u) == 0;
-  const Kernel pkernel = sort_onesweep_persistent_kernel<KT, 0>;
-  // B200LABS_SORT_IMPL=4 selects the first-generation pass kernel (kept for A/B timing)
-  static const int impl = [] {
-    const char* e = getenv("B200LABS_SORT_IMPL");
-    return e ? atoi(e) : 5;
-  }();
-  static const int pass_blocks = [] {  // CTAs per SM the pass kernel is compiled for (2: 64 registers)
-    const char* e = getenv("B200LABS_SORT_BLOCKS");
-    return e ? atoi(e) : B200_SORT_PASS_BLOCKS;
-  }();
-  const Kernel pass_first = pass_blocks == 2 ? sort_pass_kernel<KT, true, false, 2> : sort_pass_kernel<KT, true, false>;
-  const Kernel pass_mid = pass_blocks == 2 ? sort_pass_kernel<KT, false, false, 2> : sort_pass_kernel<KT, false, false>;
-  const Kernel pass_last = pass_blocks == 2 ? sort_pass_kernel<KT, false, true, 2> : sort_pass_kernel<KT, false, true>;
-  static PerDeviceOnce attr_once;
-  if (int rc = attr_once.run("sort", [&]() -> int {
-    // idempotent, so two threads racing to be first is harmless
-    B200_CUDA_OK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                      (int)sizeof(SweepSmem)));
-    B200_CUDA_OK(cudaFuncSetAttribute(pkernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                      (int)sizeof(SweepSmemPersistent)));
-    for (Kernel k : {pass_first, pass_mid, pass_last}) {
-      B200_CUDA_OK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                        (int)sizeof(PassSmem)));
-      B200_CUDA_OK(cudaFuncSetAttribute(k, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
-    }
-        return 0;
-      }))
-    return rc;
   {
     size_t want = (n / 4 + kHistThreads - 1) / kHistThreads + 1;
     // >= sms*8 blocks and <= 2^22 keys per block (32-bit shared counters stay exact)
@@ -836,31 +517,9 @@ static int sort32(const uint32_t* input, uint32_t* keys, uint32_t* tmp, size_t n
   }
   sort_scan_kernel<<<1, kRadix, 0, st>>>(sc.hist, 4);
   B200_LAUNCH_OK();
-  // pass 0 reads the caller's input (which may be a separate, untouched buffer),
-  // then the passes ping-pong tmp <-> keys and the fourth one lands in `keys`
-  const uint32_t* src = input;
-  uint32_t* dst = tmp;
-  for (int pass = 0; pass < 4; ++pass) {
-    if (impl >= 5) {
-      const Kernel k = pass == 0 ? pass_first : pass == 3 ? pass_last : pass_mid;
-      k<<<(unsigned)sc.tiles, kSortThreads, sizeof(PassSmem), st>>>(
-          src, dst, n, n_dev, pass, sc.hist + pass * kRadix, sc.lookback, sc.tickets + pass);
-    } else if (persist) {
-      size_t grid = (size_t)sms * kSortBlocksPerSm;
-      if (grid > sc.tiles) grid = sc.tiles;
-      pkernel<<<(unsigned)grid, kSortThreads, sizeof(SweepSmemPersistent), st>>>(
-          src, dst, n, n_dev, pass, sc.hist + pass * kRadix, sc.lookback, sc.tickets + pass);
-    } else {
-      // the first pass need not be stable (nothing to preserve yet): flagged as ~pass
-      kernel<<<(unsigned)sc.tiles, kSortThreads, sizeof(SweepSmem), st>>>(
-          src, dst, n, n_dev, (pass == 0 && unstable_first) ? ~pass : pass, sc.hist + pass * kRadix,
-          sc.lookback, sc.tickets + pass);
-    }
-    B200_LAUNCH_OK();
-    src = dst;
-    dst = (dst == tmp) ? keys : tmp;
-  }
-  return 0;  // four passes: the result is in `keys`
+  // n is the capacity (the upper bound on the length): below 2^32 every output index fits 32 bits
+  if (n < (size_t(1) << 32)) return sort32_passes<KT, false>(input, keys, tmp, n, n_dev, sc, st);
+  return sort32_passes<KT, true>(input, keys, tmp, n, n_dev, sc, st);
 }
 
 }  // namespace b200

@@ -14,7 +14,8 @@ from pathlib import Path
 
 PKG_DIR = Path(__file__).resolve().parent
 REPO_ROOT = PKG_DIR.parent
-LIB_PATH = PKG_DIR / "lib" / "libb200labs.so"
+# B200LABS_LIB points at another build of the library (kernel-variant experiments)
+LIB_PATH = Path(os.environ["B200LABS_LIB"]) if os.environ.get("B200LABS_LIB") else PKG_DIR / "lib" / "libb200labs.so"
 
 _lock = threading.Lock()
 _lib = None

@@ -126,6 +126,56 @@ class ShardedRoberts:
         r = self.group.rank
         return None if r == self.group.world - 1 else self.sym_in.peer_address(r + 1)
 
+    def run_host(self, host_in: torch.Tensor, host_out: torch.Tensor, chunk_bytes: int = 256 << 20) -> torch.Tensor:
+        """One end-to-end step through the product path.  This rank's band sits in pinned host
+        memory (int32 [h_local, w]); it is copied into the symmetric device band in row
+        chunks on a copy stream, each chunk is filtered as soon as it and the row after it
+        are on the GPU, and the result is copied back on a third stream, so H2D, kernel
+        and D2H of different chunks overlap.  The last chunk's kernel reads the row below
+        the band straight from the next rank's GPU over NVLink, as ``step()`` does; two
+        stream-ordered cross-GPU barriers (flags over peer memory, no host sync) bracket
+        that: one after every rank's first chunk has landed (the neighbour's first row is
+        valid), one after the last kernel (no rank refills its band while a neighbour may
+        still be reading it).  Synchronises the calling stream before returning."""
+        if self.impl != "fused":
+            raise ValueError("run_host drives the fused (peer-memory halo) path")
+        g, h, w = self.group, self.h_local, self.w
+        src = host_in.view(torch.int32).reshape(h, w)
+        dst = host_out.view(torch.int32).reshape(h, w)
+        rows = max(1, min(h, chunk_bytes // (4 * w)))
+        chunks = [(r0, min(h, r0 + rows)) for r0 in range(0, h, rows)]
+        cur = torch.cuda.current_stream(g.device)
+        if getattr(self, "_io_streams", None) is None:
+            self._io_streams = (torch.cuda.Stream(device=g.device), torch.cuda.Stream(device=g.device))
+        s_up, s_down = self._io_streams
+        s_up.wait_stream(cur)
+        s_down.wait_stream(cur)
+        landed = []
+        with torch.cuda.stream(s_up):
+            for r0, r1 in chunks:
+                self.band[r0:r1].copy_(src[r0:r1], non_blocking=True)
+                ev = torch.cuda.Event()
+                ev.record(s_up)
+                landed.append(ev)
+        peer_below = self.below_address()
+        for k, (r0, r1) in enumerate(chunks):
+            if k == 0 and g.world > 1:
+                cur.wait_event(landed[0])
+                g.device_barrier()
+            cur.wait_event(landed[min(k + 1, len(chunks) - 1)])   # row r1 belongs to the next chunk
+            below = self.band[r1] if r1 < h else peer_below
+            roberts_op(self.band[r0:r1], self.out[r0:r1], below_row=below, variant=self.variant)
+            done = torch.cuda.Event()
+            done.record(cur)
+            with torch.cuda.stream(s_down):
+                s_down.wait_event(done)
+                dst[r0:r1].copy_(self.out[r0:r1], non_blocking=True)
+        if g.world > 1:
+            g.device_barrier()
+        cur.wait_stream(s_down)
+        cur.synchronize()
+        return host_out
+
     def step(self) -> torch.Tensor:
         g = self.group
         if self.impl == "fused":

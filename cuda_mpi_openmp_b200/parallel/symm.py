@@ -62,6 +62,12 @@ class SymmetricBuffer:
     def peer_address(self, r: int, byte_offset: int = 0) -> int:
         return self.peer_ptrs[r] + byte_offset
 
+    def peer_view(self, r: int, dtype: torch.dtype, n: int, byte_offset: int = 0) -> torch.Tensor:
+        """``n`` elements of rank r's buffer as a tensor on THIS rank's device (a peer mapping:
+        reading it moves the bytes over NVLink).  For checks and small copies."""
+        nbytes = n * torch.empty((), dtype=dtype).element_size()
+        return _wrap(self.peer_ptrs[r] + byte_offset, nbytes, self.group.device).view(dtype)
+
     def free(self):
         L = N.lib()
         for p in self._opened:

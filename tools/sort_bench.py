@@ -58,7 +58,7 @@ def main():
     args = ap.parse_args()
     dev = torch.device("cuda:0")
     dtype = {"int32": torch.int32, "float32": torch.float32}[args.dtype]
-    tag = {k: os.environ.get(k, "") for k in ("B200LABS_SORT_IMPL", "B200LABS_SORT_BLOCKS")}
+    tag = {k: os.environ.get(k, "") for k in ("B200LABS_SORT_IMPL", "B200LABS_SORT_NB", "B200LABS_SORT_FIRST_BLOCKS")}
     rows = []
     for lg in [int(v) for v in args.n.split(",")]:
         n = 1 << lg
