@@ -28,6 +28,7 @@ int main() {
   CSC(cudaMemcpy(da, a.data(), bytes, cudaMemcpyHostToDevice));
   CSC(cudaMemcpy(db, b.data(), bytes, cudaMemcpyHostToDevice));
 
+  LIBOK(b200_preload_lab1());
   float ms = cli::time_device_ms([&] {
     if (grid > 0 && block > 0)
       LIBOK(b200_vecsub_f64_geom(da, db, dc, (size_t)n, grid, block, nullptr));

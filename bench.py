@@ -66,6 +66,98 @@ def peak_gbs():
         return 6650.0, "fallback"
 
 
+# ===================================================================== binaries, both arms
+def write_synthetic_image(path, w, rows, seed):
+    """`int w, int rows, RGBA[]` file of random pixels (a 1024-row random block, repeated)."""
+    import numpy as np
+
+    rng = np.random.default_rng(seed)
+    with open(path, "wb") as f:
+        f.write(np.array([w, rows], dtype=np.int32).tobytes())
+        block = rng.integers(0, 256, size=min(rows, 1024) * w * 4, dtype=np.uint8)
+        left = rows
+        while left > 0:
+            n = min(left, 1024)
+            f.write(block[: n * w * 4].tobytes())
+            left -= n
+
+
+def binary_step(exe, stdin, env, n_chunks):
+    """One step through a contract binary's stdin/file protocol: n_chunks invocations, each a fresh
+    process (spawn, CUDA context, file read, H2D, kernel, D2H, file write).  Returns (sum of the
+    binaries' own kernel ms, wall ms)."""
+    kernel_ms, t0 = 0.0, time.perf_counter()
+    for _ in range(n_chunks):
+        r = subprocess.run([str(exe)], input=stdin, capture_output=True, text=True, env=env)
+        if r.returncode != 0:
+            raise RuntimeError(f"{exe} failed: {r.stderr[-500:]}")
+        kernel_ms += float(r.stdout.split("<")[1].split(" ms>")[0])
+    return kernel_ms, (time.perf_counter() - t0) * 1e3
+
+
+def own_binary_e2e(args, group, rank, world, local_rank, w, h):
+    """The like-for-like end-to-end arm: this repository's lab2/src/to_plot_cuda_exe driven exactly
+    as bench.py drives the reference binary (same /dev/shm files, same stdin protocol, same
+    <= 2^30-pixel chunks, a fresh process per chunk), plus one run per rank on its WHOLE band
+    (64-bit sizes: the reference's int pixel index cannot do that)."""
+    import numpy as np
+
+    from cuda_mpi_openmp_b200.models import RobertsFilter
+
+    exe = ROOT / "lab2" / "src" / "to_plot_cuda_exe"
+    h_local = h // world
+    rows_per_chunk = max(1, min(h_local, (1 << 30) // w))
+    n_chunks = (h_local + rows_per_chunk - 1) // rows_per_chunk
+    shm = Path("/dev/shm") if Path("/dev/shm").is_dir() else Path("/tmp")
+    in_path, out_path = shm / f"b200own_in_{rank}.data", shm / f"b200own_out_{rank}.data"
+    env = {**os.environ, "CUDA_VISIBLE_DEVICES": str(local_rank)}
+    env.pop("B200LABS_WARM", None)
+    res, ok = {}, True
+    try:
+        for label, rows, chunks, steps in (("chunked", rows_per_chunk, n_chunks, 2), ("whole_band", h_local, 1, 1)):
+            if label == "whole_band" and n_chunks == 1:
+                res[label] = "same as chunked (the band is one chunk)"
+                continue
+            write_synthetic_image(in_path, w, rows, seed=1234 + rank)
+            stdin = f"-1\n-1\n-1\n-1\n{in_path}\n{out_path}\n"
+            group.barrier()
+            binary_step(exe, stdin, env, 1)                       # warm-up: page cache, driver files
+            group.barrier()
+            k_ms, wall = [], []
+            for _ in range(steps):
+                k, wl = binary_step(exe, stdin, env, chunks)
+                k_ms.append(k)
+                wall.append(wl)
+            my_k, my_wall = group.all_reduce_max(sum(k_ms) / steps), group.all_reduce_max(sum(wall) / steps)
+            total_bytes = BYTES_PER_PX * w * rows * chunks * world
+            res[label] = {"value": round(total_bytes / my_wall / 1e6, 3), "unit": "GB/s", "ms_per_step": round(my_wall, 1),
+                          "kernel_ms_per_step": round(my_k, 3), "steps": steps, "invocations_per_step": chunks,
+                          "rows_per_invocation": rows}
+            # the file the binary wrote, first and last 64 rows, against the CPU oracle
+            with open(in_path, "rb") as f:
+                head_in = np.frombuffer(f.read(8 + 65 * w * 4), dtype=np.uint8, offset=8).reshape(65, w, 4)
+                f.seek(8 + (rows - 64) * w * 4)
+                tail_in = np.frombuffer(f.read(64 * w * 4), dtype=np.uint8).reshape(64, w, 4)
+            with open(out_path, "rb") as f:
+                hdr = np.frombuffer(f.read(8), dtype=np.int32)
+                head_out = np.frombuffer(f.read(64 * w * 4), dtype=np.uint8).reshape(64, w, 4)
+                f.seek(8 + (rows - 64) * w * 4)
+                tail_out = np.frombuffer(f.read(64 * w * 4), dtype=np.uint8).reshape(64, w, 4)
+            size_ok = os.path.getsize(out_path) == 8 + rows * w * 4 and hdr.tolist() == [w, rows]
+            ok = ok and size_ok and bool(np.array_equal(RobertsFilter.reference(head_in)[:64], head_out)) \
+                and bool(np.array_equal(RobertsFilter.reference(tail_in), tail_out))
+    finally:
+        for p in (in_path, out_path):
+            try:
+                p.unlink()
+            except OSError:
+                pass
+    ok = bool(group.all_reduce_max(0.0 if ok else 1.0) == 0.0)
+    res["api"] = ("lab2/src/to_plot_cuda_exe through the reference's stdin/file protocol on /dev/shm: process start, "
+                  "CUDA context, file read, H2D, kernel, D2H, file write, every invocation")
+    return res, {"ok": ok, "checked": "first and last 64 rows of each output file vs CPU oracle, header, size"}
+
+
 # =============================================================================== own arm
 def fill_random_(t, seed):
     """Random bits into an int32 (or int32-viewable) device tensor, in 1 GiB pieces."""
@@ -182,6 +274,10 @@ def run_own(args):
     del model
     torch.cuda.empty_cache()
 
+    e2e_binary = None
+    if not args.no_e2e and (ROOT / "lab2" / "src" / "to_plot_cuda_exe").exists():
+        e2e_binary, verify["lab2_binary_output_vs_cpu_oracle"] = own_binary_e2e(args, group, rank, world, local_rank, w, h)
+
     # ------------------------------------------------------------ the other labs at this N
     labs = {}
     if not args.no_extras:
@@ -265,7 +361,8 @@ def run_own(args):
                                 "slower than the 2+2 GiB copy MEASURED_PEAKS.json was taken on"},
             "clocks": {"sm_mhz": clock_summary["sm_mhz"], "sm_max_mhz": clock_summary["sm_max_mhz"],
                        "reasons": clock_summary["reasons"], "samples": clock_summary["samples"]},
-            "e2e": e2e, "gpu_launches": int(launches_timed), "labs": labs, "verify": verify,
+            "e2e": e2e, "e2e_binary": e2e_binary, "gpu_launches": int(launches_timed), "labs": labs,
+            "verify": verify,
             "published_reference_note": "BASELINE.md has no published number for this config (reference numbers "
                                         "are A6000 launch-latency-bound <= 0.18 ms figures on <= 1 MP images)",
             "out_sample": flag_out_sample[0][:4],
@@ -388,26 +485,12 @@ def run_reference(args):
     n_chunks = (h_local + rows_per_chunk - 1) // rows_per_chunk
     shm = Path("/dev/shm") if Path("/dev/shm").is_dir() else Path("/tmp")
     in_path, out_path = shm / f"b200ref_in_{rank}.data", shm / f"b200ref_out_{rank}.data"
-    rng = np.random.default_rng(1234 + rank)
-    with open(in_path, "wb") as f:
-        f.write(np.array([w, rows_per_chunk], dtype=np.int32).tobytes())
-        block = rng.integers(0, 256, size=min(rows_per_chunk, 1024) * w * 4, dtype=np.uint8)
-        left = rows_per_chunk
-        while left > 0:
-            n = min(left, 1024)
-            f.write(block[: n * w * 4].tobytes())
-            left -= n
+    write_synthetic_image(in_path, w, rows_per_chunk, seed=1234 + rank)
     env = {**os.environ, "CUDA_VISIBLE_DEVICES": str(local_rank)}
     stdin = f"32\n32\n16\n16\n{in_path}\n{out_path}\n"
 
     def one_step():
-        kernel_ms, t0 = 0.0, time.perf_counter()
-        for _ in range(n_chunks):
-            r = subprocess.run([str(exe)], input=stdin, capture_output=True, text=True, env=env)
-            if r.returncode != 0:
-                raise RuntimeError(f"reference binary failed: {r.stderr[-500:]}")
-            kernel_ms += float(r.stdout.split("<")[1].split(" ms>")[0])
-        return kernel_ms, (time.perf_counter() - t0) * 1e3
+        return binary_step(exe, stdin, env, n_chunks)
 
     def barrier():
         if dist is not None:

@@ -70,6 +70,15 @@ struct PerDeviceOnce {
   }
 };
 
+// Forces the (lazily loaded) module that holds `kernel` onto the current device without
+// launching anything: what b200_preload_* is made of.
+template <typename K>
+inline int preload_kernel(K kernel) {
+  cudaFuncAttributes a;
+  B200_CUDA_OK(cudaFuncGetAttributes(&a, kernel));
+  return 0;
+}
+
 // ---- device-side PTX wrappers ---------------------------------------------
 #if defined(__CUDACC__)
 

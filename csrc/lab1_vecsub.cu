@@ -92,3 +92,8 @@ extern "C" int b200_vecsub_f64_geom(const double* a, const double* b, double* c,
   B200_LAUNCH_OK();
   return 0;
 }
+
+extern "C" int b200_preload_lab1(void) {
+  if (int rc = preload_kernel(vecsub_v4_kernel)) return rc;
+  return preload_kernel(vecsub_scalar_kernel);
+}

@@ -27,6 +27,7 @@ namespace b200 {
 int roberts_tma_launch(const void* in, void* out, int w, int64_t h_local, const void* below_row,
                        cudaStream_t st);  // lab2_roberts_tma.cu
 bool roberts_tma_supported(const void* in, const void* out, int w, int64_t h_local);
+int roberts_tma_preload();
 int roberts_cluster_launch(const void* in, void* out, int w, int64_t h_local,
                            const void* below_row, cudaStream_t st);  // lab2_roberts_cluster.cu
 bool roberts_cluster_supported(const void* in, const void* out, int w, int64_t h_local);
@@ -218,4 +219,10 @@ extern "C" int b200_roberts_geom(const void* in, void* out, int w, int h, int bx
   roberts_generic_kernel<<<dim3(gx, gy), dim3(bx, by), 0, as_stream(s)>>>(src, (uint32_t*)out);
   B200_LAUNCH_OK();
   return 0;
+}
+
+extern "C" int b200_preload_lab2(void) {
+  if (int rc = preload_kernel(roberts_generic_kernel)) return rc;
+  if (int rc = preload_kernel(roberts_stream_kernel<4>)) return rc;
+  return roberts_tma_preload();
 }

@@ -285,4 +285,6 @@ int roberts_tma_launch(const void* in, void* out, int w, int64_t h_local, const 
   return 0;
 }
 
+int roberts_tma_preload() { return preload_kernel(roberts_tma_kernel); }
+
 }  // namespace b200

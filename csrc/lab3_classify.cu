@@ -401,3 +401,15 @@ extern "C" int b200_lab3_apply_lut(void* img, int64_t npix, const void* lut, voi
 }
 
 extern "C" size_t b200_lab3_coarse_bytes(void) { return kCoarseBytes; }
+
+extern "C" int b200_preload_lab3(void) {
+  if (int rc = preload_kernel(lab3_moments_kernel)) return rc;
+  if (int rc = preload_kernel(lab3_finalize_kernel)) return rc;
+  if (int rc = preload_kernel(lab3_classify_direct_kernel)) return rc;
+  if (int rc = preload_kernel(lab3_classify_scalar_kernel)) return rc;
+  if (int rc = preload_kernel(lab3_lut_build_hoisted_kernel)) return rc;
+  if (int rc = preload_kernel(lab3_lut_apply_kernel)) return rc;
+  if (int rc = preload_kernel(lab3_lut_coarsen_kernel)) return rc;
+  if (int rc = preload_kernel(lab3_lut_apply_coarse_kernel<4>)) return rc;
+  return preload_kernel(lab3_lut_apply_scalar_kernel);
+}

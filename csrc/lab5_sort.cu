@@ -701,3 +701,24 @@ extern "C" int b200_sort_noalloc(const void* input, void* output, size_t n, int 
     }
   }
 }
+
+extern "C" int b200_preload_lab5(int key_type) {
+  auto passes = [](auto kt) -> int {
+    constexpr int KT = decltype(kt)::value;
+    if (int rc = preload_kernel(sort_hist_kernel<KT>)) return rc;
+    if (int rc = preload_kernel(sort_pass_kernel<KT, true, false, false>)) return rc;
+    if (int rc = preload_kernel(sort_pass_kernel<KT, false, false, false>)) return rc;
+    return preload_kernel(sort_pass_kernel<KT, false, true, false>);
+  };
+  if (int rc = preload_kernel(sort_scan_kernel)) return rc;
+  switch (key_type) {
+    case B200_KEY_I32: return passes(std::integral_constant<int, B200_KEY_I32>());
+    case B200_KEY_U32: return passes(std::integral_constant<int, B200_KEY_U32>());
+    case B200_KEY_F32: return passes(std::integral_constant<int, B200_KEY_F32>());
+    case B200_KEY_U8:
+      if (int rc = preload_kernel(sort_u8_hist_kernel)) return rc;
+      return preload_kernel(sort_u8_fill_kernel);
+    default: B200_REQUIRE(false, "preload: unknown key type %d", key_type);
+  }
+  return 0;
+}

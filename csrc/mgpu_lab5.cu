@@ -71,10 +71,12 @@ __global__ void __launch_bounds__(kSplitThreads)
                           int samples_per_rank, int idx_bits, SymmPeers peers, int rank, int world,
                           uint64_t epoch, uint32_t seed, int phase_mask,
                           unsigned long long timeout_ns) {
-  extern __shared__ unsigned long long sm[];  // world * samples_per_rank composites
+  extern __shared__ unsigned long long sm[];  // world * samples_per_rank composites, padded to 2^k
   SymmWorkspace* me = peers.ws[rank];
   const int tid = threadIdx.x;
   const int total = world * samples_per_rank;
+  int padded = 1;  // the bitonic network needs a power of two: any world size is padded with
+  while (padded < total) padded <<= 1;  // composites that sort last
 
   if (phase_mask & 1) {
     if (tid == 0) {
@@ -105,16 +107,17 @@ __global__ void __launch_bounds__(kSplitThreads)
   if (phase_mask & 2) {
     if (tid < world) wait_peer(peers, rank, tid, epoch, timeout_ns, kFlagSortSamples);
     __syncthreads();
-    // bitonic sort of `total` (power of two) composites in shared memory
-    for (int i = tid; i < total; i += kSplitThreads) {
-      unsigned long long v;
-      asm volatile("ld.global.cg.u64 %0, [%1];" : "=l"(v) : "l"(me->sort_samples + i) : "memory");
+    // bitonic sort of the composites in shared memory
+    for (int i = tid; i < padded; i += kSplitThreads) {
+      unsigned long long v = ~0ull;
+      if (i < total)
+        asm volatile("ld.global.cg.u64 %0, [%1];" : "=l"(v) : "l"(me->sort_samples + i) : "memory");
       sm[i] = v;
     }
     __syncthreads();
-    for (int k = 2; k <= total; k <<= 1) {
+    for (int k = 2; k <= padded; k <<= 1) {
       for (int j = k >> 1; j > 0; j >>= 1) {
-        for (int i = tid; i < total; i += kSplitThreads) {
+        for (int i = tid; i < padded; i += kSplitThreads) {
           const int ixj = i ^ j;
           if (ixj > i) {
             const unsigned long long a = sm[i], b = sm[ixj];
@@ -498,7 +501,7 @@ static int idx_bits_for(int world) {
 }
 
 // Step 1 of the multi-GPU sort: sample, exchange, choose splitters (left in
-// ws[rank]->sort_splitters).  samples_per_rank * world must be a power of two <= 8192.
+// ws[rank]->sort_splitters).  samples_per_rank * world <= 8192; any world size up to 8.
 extern "C" int b200_sort_mgpu_splitters(const void* keys, size_t n_local, int key_type,
                                         int samples_per_rank, const void* ws_ptrs, int rank,
                                         int world, uint64_t epoch, int phase_mask,
@@ -506,13 +509,15 @@ extern "C" int b200_sort_mgpu_splitters(const void* keys, size_t n_local, int ke
   B200_REQUIRE(world >= 1 && world <= kMaxWorld && rank >= 0 && rank < world,
                "sort_mgpu: bad rank/world %d/%d", rank, world);
   const int total = world * samples_per_rank;
-  B200_REQUIRE(samples_per_rank > 0 && total <= kSortMaxSamplesTotal && (total & (total - 1)) == 0,
-               "sort_mgpu: world*samples_per_rank must be a power of two <= %d (got %d)",
-               kSortMaxSamplesTotal, total);
+  B200_REQUIRE(samples_per_rank > 0 && total <= kSortMaxSamplesTotal,
+               "sort_mgpu: world*samples_per_rank must be at most %d (got %d)", kSortMaxSamplesTotal,
+               total);
   const int idx_bits = idx_bits_for(world);
   B200_REQUIRE(idx_bits >= 32 || n_local <= (1ull << idx_bits), "sort_mgpu: shard too large");
   SymmPeers peers{(SymmWorkspace* const*)ws_ptrs};
-  const size_t smem = (size_t)total * sizeof(unsigned long long);
+  size_t padded = 1;
+  while (padded < (size_t)total) padded <<= 1;
+  const size_t smem = padded * sizeof(unsigned long long);
   cudaStream_t st = as_stream(s);
 #define LAUNCH_SPLIT(KT)                                                                       \
   do {                                                                                         \

@@ -339,30 +339,49 @@ def sort_devn(bucket: torch.Tensor, tmp: torch.Tensor, count_addr: int, scratch:
 
 
 def samples_per_rank_for(world: int) -> int:
-    return 8192 // world if world & (world - 1) == 0 else 1 << int(np.log2(8192 // world))
+    """Samples each rank contributes to the splitter selection: as many as fit the 8192-entry
+    sample area (the kernel pads the total to a power of two for its sorting network)."""
+    return 8192 // world
+
+
+ERR_TIMEOUT, ERR_SORT_OVERFLOW = 1, 2     # SymmError bits of the workspace's sticky error word
+
+
+def raise_on_error(group: PeerGroup, what: str) -> int:
+    """Reads this rank's sticky error word (a device-to-host copy: call at a point where the
+    stream may be synchronised) and raises if an in-kernel wait for a peer timed out — after
+    a timeout every number derived from that peer's data is garbage.  Returns the word."""
+    err = group.ws_error()
+    if err & ERR_TIMEOUT:
+        raise RuntimeError(f"{what}: rank {group.rank} timed out waiting for a peer inside a kernel "
+                           f"(error word {err:#x}); results of this step are invalid")
+    return err
 
 
 class ShardedSort:
-    """Sample sort over the ranks.  After ``step()`` rank r holds the r-th slice of the
-    globally sorted sequence in ``bucket[:count()]``."""
+    """Sample sort over the ranks (any world size up to 8).  After ``step()`` rank r holds the
+    r-th slice of the globally sorted sequence in ``result()`` (= ``bucket[:count()]``).
+
+    ``step()`` only enqueues work.  ``count()`` / ``result()`` are COLLECTIVE sync points: they
+    read the error word of every rank, raise if a peer wait timed out, and if any
+    destination bucket overflowed (the kernels never write out of bounds: they drop the excess
+    and set the overflow bit) they grow the buckets on every rank and run the step again —
+    doubling until nothing overflows, which must happen by capacity = all keys.  Keys are
+    never lost; until ``count()``/``result()`` has returned, ``bucket`` must be treated as
+    not final."""
 
     SLACK = 1.25
 
     def __init__(self, group: PeerGroup, n_local: int, dtype: torch.dtype = torch.int32, impl: str = "fused"):
         assert impl in ("fused", "nccl")
-        if group.world & (group.world - 1):
-            raise ValueError("ShardedSort needs a power-of-two number of ranks")
         self.group, self.n_local, self.dtype, self.impl = group, n_local, dtype, impl
         dev, world = group.device, group.world
         self.keys = torch.empty(n_local, dtype=dtype, device=dev)
-        self.capacity = n_local if world == 1 else int(n_local * self.SLACK) + 8192
-        self.sym_bucket = group.alloc(self.capacity * 4)
-        self.bucket = self.sym_bucket.view(dtype, self.capacity)
-        self.tmp = torch.empty(self.capacity, dtype=dtype, device=dev)
-        self.scratch = torch.empty(ST.sort_scratch_bytes(self.capacity, dtype), dtype=torch.uint8, device=dev)
         self.ws = group.workspace()
         self.samples = samples_per_rank_for(world)
-        self._off = {k: group.ws_offset(k) for k in ("sort_splitters", "sort_recv_count", "sort_cursor")}
+        self._off = {k: group.ws_offset(k) for k in ("sort_splitters", "sort_recv_count", "sort_cursor", "error")}
+        self.sym_bucket = None
+        self._allocate(n_local if world == 1 else int(n_local * self.SLACK) + 8192)
         if impl == "nccl" and world > 1:
             self.send = torch.empty((world, n_local), dtype=dtype, device=dev)
             self.cursors = torch.zeros(world, dtype=torch.int64, device=dev)
@@ -375,10 +394,52 @@ class ShardedSort:
         self.reserve = os.environ.get("B200LABS_SORT_RESERVE", "0") == "1"
         self.launches_per_step = (6 if world == 1 else 9 if self.reserve else 8)
         self._count_host: Optional[int] = None
+        self._settled = False
+        self.retries = 0
+
+    def _allocate(self, capacity: int) -> None:
+        """(Re)allocates bucket, ping-pong buffer and sort scratch for ``capacity`` keys.  Collective."""
+        g = self.group
+        if self.sym_bucket is not None:
+            self.bucket = self.tmp = self.scratch = None
+            g.barrier()
+            self.sym_bucket.free()
+        self.capacity = int(capacity)
+        self.sym_bucket = g.alloc(self.capacity * 4)
+        self.bucket = self.sym_bucket.view(self.dtype, self.capacity)
+        self.tmp = torch.empty(self.capacity, dtype=self.dtype, device=g.device)
+        self.scratch = torch.empty(ST.sort_scratch_bytes(self.capacity, self.dtype), dtype=torch.uint8,
+                                   device=g.device)
+
+    def _settle(self) -> None:
+        """Collective check of the step just run; grows the buckets and re-runs on overflow."""
+        if self._settled:
+            return
+        g = self.group
+        while True:
+            torch.cuda.synchronize(g.device)
+            err = raise_on_error(g, "ShardedSort") if g.world > 1 else 0
+            overflow = g.all_reduce_max(1.0 if err & ERR_SORT_OVERFLOW else 0.0) > 0 if g.world > 1 else False
+            if not overflow:
+                break
+            n_total = int(g.all_reduce_max(float(self.n_local))) * g.world      # upper bound on any bucket
+            if self.capacity >= n_total:
+                raise RuntimeError("ShardedSort: bucket overflow with capacity for every key (corrupt workspace?)")
+            off = self._off["error"]                     # clear the sticky overflow bit, keep nothing else set
+            self.ws.local[off: off + 8].view(torch.int64).zero_()
+            self._allocate(min(2 * self.capacity, n_total))
+            self.retries += 1
+            self._count_host = None
+            self._run()
+        self._settled = True
 
     def step(self) -> None:
-        g, world, r = self.group, self.group.world, self.group.rank
         self._count_host = None
+        self._settled = False
+        self._run()
+
+    def _run(self) -> None:
+        g, world, r = self.group, self.group.world, self.group.rank
         if world == 1:
             # out of place: pass 0 reads `keys`, the result lands in `bucket`
             N.check(N.lib().b200_sort_ex(N.ptr(self.keys), N.ptr(self.bucket), N.ptr(self.tmp), self.n_local,
@@ -406,8 +467,10 @@ class ShardedSort:
         dist.all_to_all_single(recv_counts, self.cursors, group=g.pg)
         send_n, recv_n = self.cursors.tolist(), recv_counts.tolist()
         total = int(sum(recv_n))
-        if total > self.capacity:
-            raise RuntimeError(f"rank {r}: bucket overflow ({total} > {self.capacity})")
+        need = int(g.all_reduce_max(float(total)))      # the exchange has not happened yet: just grow
+        if need > self.capacity:
+            self._allocate(need)
+            self.retries += 1
         outs, o = [], 0
         for d in range(world):
             outs.append(self.bucket[o: o + recv_n[d]])
@@ -422,6 +485,7 @@ class ShardedSort:
         self.sym_bucket.free()
 
     def count(self) -> int:
+        self._settle()
         if self._count_host is None:
             off = self._off["sort_recv_count"]
             self._count_host = int(self.ws.local[off: off + 8].view(torch.int64).item())

@@ -139,6 +139,49 @@ def main():
                     assert np.array_equal(got, allk), f"sort {impl} {dt}"
                     sizes = [b.size for _, b in gathered]
                     assert max(sizes) <= m.capacity
+    # ---- adversarial inputs for the fused sort: nothing may be lost, whatever the distribution
+    def check_sorted_multiset(m, k, tag):
+        g.barrier()
+        m.step()
+        mine = m.result().cpu().numpy()                  # collective: settles (and retries) the step
+        assert g.ws_error() == 0, f"{tag}: error word {g.ws_error()}"
+        gathered = [None] * world
+        dist.all_gather_object(gathered, (k, mine))
+        if rank == 0:
+            allk = np.sort(np.concatenate([a for a, _ in gathered]))
+            got = np.concatenate([b for _, b in gathered])
+            assert got.size == allk.size, f"{tag}: {allk.size - got.size} keys lost"
+            assert np.array_equal(got, allk), tag
+
+    n_adv = 200_000 + 7
+    m = ShardedSort(g, n_adv, torch.int32)
+    cases = {
+        "all_equal": np.full(n_adv, 42, dtype=np.int32),
+        "one_ranks_range": (np.random.default_rng(rank).integers(0, 1000, n_adv)).astype(np.int32),
+        "presorted_shards": np.sort(np.random.default_rng(7 + rank).integers(-2**31, 2**31 - 1, n_adv)).astype(np.int32),
+        "disjoint_ranges": (np.random.default_rng(rank).integers(0, 1 << 20, n_adv) + (rank << 24)).astype(np.int32),
+    }
+    for tag, k in cases.items():
+        m.keys.copy_(torch.from_numpy(k))
+        check_sorted_multiset(m, k, tag)
+    assert m.retries == 0, "the unique-composite splitters keep every one of these balanced"
+    g.barrier()
+    m.free()
+    # buckets far too small: the step overflows, result() grows them on every rank and re-runs
+    old_slack, ShardedSort.SLACK = ShardedSort.SLACK, 0.4
+    try:
+        m = ShardedSort(g, n_adv, torch.int32)
+        k = np.random.default_rng(99 + rank).integers(-2**31, 2**31 - 1, n_adv).astype(np.int32)
+        m.keys.copy_(torch.from_numpy(k))
+        check_sorted_multiset(m, k, "forced_overflow")
+        assert m.retries >= 1 and m.capacity >= n_adv * 0.8
+        check_sorted_multiset(m, k, "after_growth")      # the grown buckets keep working
+        g.barrier()
+        m.free()
+    finally:
+        ShardedSort.SLACK = old_slack
+    if rank == 0:
+        print("SORT_ADVERSARIAL_OK (all equal, one range, presorted, disjoint, forced overflow -> retry)")
     g.barrier()
     if rank == 0:
         print("MP_WORKER_OK world", world)

@@ -42,7 +42,7 @@ def test_lab1_cuda_binaries(built, cuda_device):
     assert bad.returncode == 1 and "[ERROR CUDA]" in bad.stderr
 
 
-@pytest.mark.parametrize("env", [{}, {"B200LABS_ROBERTS": "generic"}, {"B200LABS_COLD": "1"}])
+@pytest.mark.parametrize("env", [{}, {"B200LABS_ROBERTS": "generic"}, {"B200LABS_WARM": "1"}])
 def test_lab2_cuda_binaries(built, cuda_device, tmp_path, env):
     for name in ("test_01", "test_02"):
         src = ImgData(str(built / "lab2/data" / f"{name}.txt"), out_dir=str(tmp_path))
@@ -88,6 +88,43 @@ def test_lab5_cuda_binaries(built, cuda_device, tmp_path):
     assert r.stdout.startswith("CUDA execution time: <"), r.stderr
     got = np.frombuffer((tmp_path / "sorted").read_bytes(), dtype=np.int32, offset=4)
     assert np.array_equal(got, np.sort(keys))
+
+
+def test_large_files_take_the_pipelined_path(built, cuda_device, tmp_path):
+    """Payloads of 32 MiB and more are streamed file -> pinned ring -> GPU -> pinned ring -> file by
+    several I/O threads (apps/cli_pipeline.h); the bytes must be the ones the plain path writes."""
+    rng = np.random.default_rng(9)
+    img = rng.integers(0, 256, size=(2900, 3004, 4), dtype=np.uint8)         # 34.8 MB, odd chunk tail
+    p, out = tmp_path / "big.data", tmp_path / "big_out.data"
+    p.write_bytes(encode_data_bytes(img))
+    r = run(built / "lab2/src/to_plot_cuda_exe", f"-1\n-1\n-1\n-1\n{p}\n{out}")
+    assert r.returncode == 0 and r.stdout.endswith("FINISHED!\n"), r.stderr
+    assert np.array_equal(ImgData(str(out), materialize=False).rgba, RobertsFilter.reference(img))
+    # in == out forces the plain path (reading must finish before the file is truncated)
+    r = run(built / "lab2/src/cuda_exe", f"{p}\n{p}")
+    assert r.returncode == 0 and p.read_bytes() == out.read_bytes()
+    # lab3: same image, classes from random points; piped output == host-statistics-free plain path
+    p.write_bytes(encode_data_bytes(img))
+    pts = "\n".join("50 " + " ".join(f"{x} {y}" for x, y in zip(rng.integers(0, 3004, 50), rng.integers(0, 2900, 50)))
+                    for _ in range(5))
+    r = run(built / "lab3/src/cuda_exe", f"{p}\n{out}\n5\n{pts}")
+    assert r.returncode == 0, r.stderr
+    got = ImgData(str(out), materialize=False).rgba
+    small = tmp_path / "same_in_out.data"
+    small.write_bytes(encode_data_bytes(img))
+    r = run(built / "lab3/src/cuda_exe", f"{small}\n{small}\n5\n{pts}")          # in == out: plain path
+    assert r.returncode == 0, r.stderr
+    assert np.array_equal(got, ImgData(str(small), materialize=False).rgba)
+    assert np.array_equal(got[..., :3], img[..., :3]) and got[..., 3].max() < 5
+    # lab5: 9 M keys = 36 MB
+    keys = rng.integers(-2**31, 2**31 - 1, 9_000_001, dtype=np.int64).astype(np.int32)
+    kp = tmp_path / "int_huge"
+    kp.write_bytes(struct.pack("<i", keys.size) + keys.tobytes())
+    r = run(built / "lab5/src/to_plot_cuda_exe", f"1\n1\n{kp}\n{tmp_path / 'sorted_huge'}\nint")
+    assert r.returncode == 0 and r.stdout.startswith("CUDA execution time: <"), r.stderr
+    raw = (tmp_path / "sorted_huge").read_bytes()
+    assert struct.unpack("<i", raw[:4])[0] == keys.size and len(raw) == 4 + 4 * keys.size
+    assert np.array_equal(np.frombuffer(raw, dtype=np.int32, offset=4), np.sort(keys))
 
 
 @pytest.mark.parametrize("lab,exe,sizes,extra", [

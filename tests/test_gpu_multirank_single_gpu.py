@@ -99,7 +99,7 @@ def test_lab3_cooperative_lut_matches_oracle(cuda_device, world):
         b.free()
 
 
-@pytest.mark.parametrize("world", [2, 4, 8])
+@pytest.mark.parametrize("world", [2, 3, 4, 6, 8])
 @pytest.mark.parametrize("dtype,kind", [(np.int32, "random"), (np.float32, "random"), (np.int32, "dups"),
                                         (np.int32, "equal"), (np.uint32, "skewed")])
 def test_sample_sort_fused_scatter(cuda_device, world, dtype, kind):

@@ -61,8 +61,9 @@ def main():
     out = ROOT / "gpurun_out" / "harness_sweep.json"
     out.parent.mkdir(exist_ok=True)
     for lab, ours, ref, sizes, k, extra in plans:
-        res[f"{lab}.ours.warm"] = sweep(ROOT / lab / "src" / ours, sizes, k, extra)
-        res[f"{lab}.ours.cold"] = sweep(ROOT / lab / "src" / ours, sizes, k, extra, {"B200LABS_COLD": "1"})
+        # default = one cold launch, timed like the reference times itself; warm = after a warm-up
+        res[f"{lab}.ours.cold"] = sweep(ROOT / lab / "src" / ours, sizes, k, extra)
+        res[f"{lab}.ours.warm"] = sweep(ROOT / lab / "src" / ours, sizes, k, extra, {"B200LABS_WARM": "1"})
         link = link_reference(lab, ref)
         if link is not None:
             res[f"{lab}.reference"] = sweep(link, sizes, k, extra)
