@@ -32,6 +32,9 @@ CPU_BINS  := lab1/src/cpu_exe lab1/src/cpu_exe_to_plot lab2/src/cpu_exe lab3/src
              lab3/src/test_read_input lab5/src/cpu_exe_int lab5/src/cpu_exe_float \
              lab5/src/cpu_exe_uchar lab5/src/to_plot_cpu_exe hw1/src/hw1 hw2/src/hw2
 
+# the binaries' directories hold nothing that is tracked, so a fresh checkout lacks them
+$(shell mkdir -p lab1/src lab2/src lab3/src lab5/src hw1/src hw2/src gpu_info/src)
+
 .PHONY: all lib bins cpu clean sass
 all: lib bins
 lib: $(SO) $(AR_LIB)
