@@ -46,7 +46,6 @@ def parse_args():
     ap.add_argument("--size", type=int, default=65536, help="image edge in pixels (w = h)")
     ap.add_argument("--variant", default="auto", help="lab2 kernel variant (auto|tma|stream|generic)")
     ap.add_argument("--exchange", choices=["fused", "nccl"], default="fused")
-    ap.add_argument("--lab3-nvls", action="store_true", help="extras: also time the NVLS (multimem) statistics")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-extras", action="store_true")
     ap.add_argument("--e2e-steps", type=int, default=None)
@@ -315,16 +314,19 @@ def run_own(args):
         t = timed_steps(group, m3.fit, 20, 3)
         labs["lab3_stats_allreduce_32x4096pts"] = {"ms": round(t, 4)}
         verify["lab3"] = verify_lab3(group, m3, classes, s3)
-        if args.lab3_nvls and world > 1:
+        labs["lab3_stats_allreduce_32x4096pts"]["path"] = (
+            "nvls (multimem.red)" if getattr(m3, "nvls", False) else "p2p stores" if args.exchange == "fused" else "nccl")
+        if world > 1 and args.exchange == "fused":     # the other in-kernel all-reduce, for the record
+            other = "p2p" if m3.nvls else "nvls"
             try:
-                m3n = ShardedClassifier(group, s3, s3, classes, impl="nvls")
-                m3n.band.copy_(m3.band)
-                t = timed_steps(group, m3n.fit, 20, 3)
-                same = bool(torch.equal(m3n.params.view(torch.int64), m3.params.view(torch.int64)))
-                labs["lab3_stats_allreduce_nvls"] = {"ms": round(t, 4), "bit_identical_to_p2p": same}
-                m3n.free()
+                m3o = ShardedClassifier(group, s3, s3, classes, impl=other)
+                m3o.band.copy_(m3.band)
+                t = timed_steps(group, m3o.fit, 20, 3)
+                same = bool(torch.equal(m3o.params.view(torch.int64), m3.params.view(torch.int64)))
+                labs[f"lab3_stats_allreduce_{other}"] = {"ms": round(t, 4), "bit_identical": same}
+                m3o.free()
             except Exception as exc:  # noqa: BLE001
-                labs["lab3_stats_allreduce_nvls"] = {"unavailable": str(exc)[:200]}
+                labs[f"lab3_stats_allreduce_{other}"] = {"unavailable": str(exc)[:200]}
         group.barrier()
         m3.free()
         del m3

@@ -133,6 +133,21 @@ __global__ void __launch_bounds__(kLutThreads)
   lut_build_block(S, nc, params, g, r0, 0, 256, [&](uint32_t id, uint8_t cls) { lut[id] = cls; });
 }
 
+// LUT + cell table in one pass (see lut_build_cells_cta): one CTA per (B chunk, G cell, 64 R)
+__global__ void __launch_bounds__(kLutThreads)
+    lab3_lut_build2_kernel(uint8_t* __restrict__ lut, uint8_t* __restrict__ cells, int nc,
+                           const double* __restrict__ params) {
+  extern __shared__ __align__(16) uint8_t lut_smem_raw[];
+  Lut2Smem& S = *reinterpret_cast<Lut2Smem*>(lut_smem_raw);
+  const int rblock = blockIdx.x & 3, gcell = (blockIdx.x >> 2) & 63, chunk = blockIdx.x >> 8;
+  lut_build_cells_cta(
+      S, nc, params, gcell, rblock * kLutR, chunk * kLut2B,
+      [&](uint32_t id, const uint4& v) { *reinterpret_cast<uint4*>(lut + id) = v; },
+      [&](uint32_t idx, const uint4& v) {
+        if (cells) *reinterpret_cast<uint4*>(cells + idx) = v;
+      });
+}
+
 __device__ __forceinline__ uint32_t lut_gather(const uint8_t* p) {
 #ifdef B200_LUT_GATHER_LDG
   return __ldg(p);
@@ -239,7 +254,7 @@ constexpr int64_t kLutMinPixels = int64_t(1) << 25;
 // Image pass against a complete table.  `coarse` (kCoarseBytes, may be null) is filled
 // here and enables the two-level kernel; B200LABS_LAB3_COARSE=0 forces the plain one.
 static int run_lut_apply(uint32_t* img, int64_t npix, const uint8_t* lut, uint8_t* coarse,
-                         cudaStream_t st) {
+                         cudaStream_t st, bool coarse_ready = false) {
   const int sms = device_info().sm_count;
   const bool aligned = (((uintptr_t)img) & 15u) == 0;
   const int64_t n_vec = aligned ? npix / 4 : 0;
@@ -265,9 +280,11 @@ static int run_lut_apply(uint32_t* img, int64_t npix, const uint8_t* lut, uint8_
           return 0;
         }))
       return rc;
-    lab3_lut_coarsen_kernel<<<(unsigned)(kCoarseBytes / 256), 256, 0, st>>>((const uint32_t*)lut,
-                                                                           coarse);
-    B200_LAUNCH_OK();
+    if (!coarse_ready) {  // the table came without its cell table: derive it
+      lab3_lut_coarsen_kernel<<<(unsigned)(kCoarseBytes / 256), 256, 0, st>>>((const uint32_t*)lut,
+                                                                             coarse);
+      B200_LAUNCH_OK();
+    }
     lab3_lut_apply_coarse_kernel<4><<<grid_for(n_vec, kApplyThreads, 1), kApplyThreads,
                                       kCoarseBytes, st>>>(img, n_vec, lut, coarse);
     B200_LAUNCH_OK();
@@ -343,28 +360,34 @@ extern "C" int b200_lab3_classify(void* img, int64_t npix, int nc, const double*
   if (variant == B200_CLASSIFY_LUT) {
     B200_REQUIRE(scratch_bytes >= kLutBytes, "lab3: LUT variant needs %zu bytes of scratch",
                  kLutBytes);
-    static const bool plain_build = [] {
+    // B200LABS_LAB3_LUT_BUILD=plain | hoisted select the older builds (table only, cells derived
+    // by a separate pass); default: table and cell table from one kernel
+    static const int build_mode = [] {
       const char* e = getenv("B200LABS_LAB3_LUT_BUILD");
-      return e && !strcmp(e, "plain");
+      return !e ? 2 : !strcmp(e, "plain") ? 0 : !strcmp(e, "hoisted") ? 1 : 2;
     }();
-    if (plain_build) {
+    uint8_t* coarse = scratch_bytes >= kLutBytes + kCoarseBytes ? (uint8_t*)scratch + kLutBytes : nullptr;
+    static PerDeviceOnce attr_once;
+    if (int rc = attr_once.run("lab3", [&]() -> int {
+          B200_CUDA_OK(cudaFuncSetAttribute(lab3_lut_build_hoisted_kernel,
+                                            cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(LutSmem)));
+          B200_CUDA_OK(cudaFuncSetAttribute(lab3_lut_build2_kernel,
+                                            cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Lut2Smem)));
+          return 0;
+        }))
+      return rc;
+    if (build_mode == 0) {
       lab3_lut_build_kernel<<<(1 << 22) / kClsThreads, kClsThreads, 0, st>>>((uint32_t*)scratch, nc,
                                                                              params);
-    } else {
-      static PerDeviceOnce attr_once;
-      if (int rc = attr_once.run("lab3", [&]() -> int {
-        B200_CUDA_OK(cudaFuncSetAttribute(lab3_lut_build_hoisted_kernel,
-                                          cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                          (int)sizeof(LutSmem)));
-            return 0;
-          }))
-        return rc;
+    } else if (build_mode == 1) {
       lab3_lut_build_hoisted_kernel<<<256 * (256 / kLutR), kLutThreads, sizeof(LutSmem), st>>>(
           (uint8_t*)scratch, nc, params);
+    } else {
+      lab3_lut_build2_kernel<<<(256 / kLut2B) * 64 * 4, kLutThreads, sizeof(Lut2Smem), st>>>(
+          (uint8_t*)scratch, coarse, nc, params);
     }
     B200_LAUNCH_OK();
-    uint8_t* coarse = scratch_bytes >= kLutBytes + kCoarseBytes ? (uint8_t*)scratch + kLutBytes : nullptr;
-    return run_lut_apply((uint32_t*)img, npix, (const uint8_t*)scratch, coarse, st);
+    return run_lut_apply((uint32_t*)img, npix, (const uint8_t*)scratch, coarse, st, build_mode == 2);
   }
   B200_REQUIRE(variant == B200_CLASSIFY_DIRECT, "lab3: unknown classify variant %d", variant);
   if (n_vec) {
@@ -402,12 +425,21 @@ extern "C" int b200_lab3_apply_lut(void* img, int64_t npix, const void* lut, voi
 
 extern "C" size_t b200_lab3_coarse_bytes(void) { return kCoarseBytes; }
 
+// Image pass against a table buffer that already holds its cell table behind the colour
+// table (b200_lab3_lut_build2_allgather): no derivation pass.
+extern "C" int b200_lab3_apply_lut2(void* img, int64_t npix, const void* lut_and_cells, b200_stream_t s) {
+  if (npix <= 0) return 0;
+  const uint8_t* lut = (const uint8_t*)lut_and_cells;
+  return run_lut_apply((uint32_t*)img, npix, lut, const_cast<uint8_t*>(lut) + kLutBytes, as_stream(s), true);
+}
+
 extern "C" int b200_preload_lab3(void) {
   if (int rc = preload_kernel(lab3_moments_kernel)) return rc;
   if (int rc = preload_kernel(lab3_finalize_kernel)) return rc;
   if (int rc = preload_kernel(lab3_classify_direct_kernel)) return rc;
   if (int rc = preload_kernel(lab3_classify_scalar_kernel)) return rc;
   if (int rc = preload_kernel(lab3_lut_build_hoisted_kernel)) return rc;
+  if (int rc = preload_kernel(lab3_lut_build2_kernel)) return rc;
   if (int rc = preload_kernel(lab3_lut_apply_kernel)) return rc;
   if (int rc = preload_kernel(lab3_lut_coarsen_kernel)) return rc;
   if (int rc = preload_kernel(lab3_lut_apply_coarse_kernel<4>)) return rc;

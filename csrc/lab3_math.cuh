@@ -157,4 +157,104 @@ __device__ __forceinline__ void lut_build_block(LutSmem& S, int nc, const double
   }
 }
 
+// ---- colour table AND cell table in one pass ---------------------------------------------
+// A CTA owns a block of colours made of WHOLE 4x4x8 cells: 64 R values x 4 G values (one G
+// cell) x 32 B values.  It classifies them G by G with the hoisted chain above (the B - mu2
+// terms of all classes come from a small shared table: 7 instead of 8 fp64-pipe operations
+// per colour and class), keeps the 8192 class bytes in shared memory, derives the 64 cell
+// bytes from them (uniform class, or kCellMixed) and hands everything out as 16-BYTE pieces:
+// 512 pieces of 16 consecutive R values and 4 pieces of 16 cells.  One piece = one 128-bit
+// store - or one multimem.st that the NVSwitch replicates into every GPU's table - where the
+// older build wrote single bytes to every peer.  No coarsening pass over the finished table.
+constexpr int kLut2B = 32;              // B values per CTA (four cells deep)
+constexpr uint32_t kCellMixed = 0xffu;  // never a class index (classes <= 32)
+struct Lut2Smem {
+  double u[kMaxC][3][kLutR];  // hoisted terms of the current G
+  double d2[kMaxC][kLut2B];   // B - mu2 per class
+  double sp[kMaxC * kNP];
+  alignas(16) uint8_t stage[4][kLut2B][kLutR];  // class bytes: 4 G x 32 B x 64 R
+  alignas(16) uint8_t cells[kLut2B / 8][kLutR / 4];
+};
+
+// The 256 B values are eight chunks of kLut2B; rank r of `world` owns chunks r, r + world, ...
+__host__ __device__ inline int lut2_chunks_of(int rank, int world) {
+  return (256 / kLut2B - rank + world - 1) / world;
+}
+
+// emit_colours(colour id of the first of 16 consecutive R values, 16 class bytes)
+// emit_cells(cell index of the first of 16 consecutive R cells, 16 cell bytes)
+template <typename EmitColours, typename EmitCells>
+__device__ __forceinline__ void lut_build_cells_cta(Lut2Smem& S, int nc, const double* __restrict__ params,
+                                                    int gcell, int r0, int b_base, EmitColours emit_colours,
+                                                    EmitCells emit_cells) {
+  static_assert(kLutThreads == 256 && kLutR == 64 && kLut2B == 32 && kLutBGroup == 8,
+                "task layout below: 256 threads = 64 R x 4 groups of 8 B");
+  const int tid = threadIdx.x;
+  for (int i = tid; i < nc * kNP; i += kLutThreads) S.sp[i] = params[i];
+  __syncthreads();
+  for (int i = tid; i < nc * kLut2B; i += kLutThreads) {
+    const int c = i / kLut2B, b = i - c * kLut2B;
+    S.d2[c][b] = __dsub_rn((double)(b_base + b), S.sp[c * kNP + 2]);
+  }
+  const int r = tid & (kLutR - 1), bg = tid / kLutR;  // this thread: one R, eight B values
+  for (int gi = 0; gi < 4; ++gi) {
+    const int g = gcell * 4 + gi;
+    __syncthreads();  // the previous G's classify loop is done with S.u (and S.d2 is complete)
+    for (int i = tid; i < nc * kLutR; i += kLutThreads) {
+      const int c = i / kLutR, rr = i - c * kLutR;
+      const double* p = S.sp + c * kNP;
+      const double d0 = __dsub_rn((double)(r0 + rr), p[0]);
+      const double d1 = __dsub_rn((double)g, p[1]);
+#pragma unroll
+      for (int k = 0; k < 3; ++k) S.u[c][k][rr] = __fma_rn(d1, p[6 + k], __fma_rn(d0, p[3 + k], 0.0));
+    }
+    __syncthreads();
+    double mind[kLutBGroup];
+    int best[kLutBGroup];
+#pragma unroll
+    for (int j = 0; j < kLutBGroup; ++j) mind[j] = DBL_MAX, best[j] = -1;
+    for (int c = 0; c < nc; ++c) {
+      const double* p = S.sp + c * kNP;
+      const double u0 = S.u[c][0][r], u1 = S.u[c][1][r], u2 = S.u[c][2][r];
+      const double d0 = __dsub_rn((double)(r0 + r), p[0]), d1 = __dsub_rn((double)g, p[1]);
+      const double m20 = p[9], m21 = p[10], m22 = p[11];
+#pragma unroll
+      for (int j = 0; j < kLutBGroup; ++j) {
+        const double d2 = S.d2[c][bg * kLutBGroup + j];
+        const double t0 = __fma_rn(d2, m20, u0), t1 = __fma_rn(d2, m21, u1), t2 = __fma_rn(d2, m22, u2);
+        double dist = __fma_rn(d0, t0, 0.0);
+        dist = __fma_rn(d1, t1, dist);
+        dist = __fma_rn(d2, t2, dist);
+        if (dist < mind[j]) mind[j] = dist, best[j] = c;
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < kLutBGroup; ++j) S.stage[gi][bg * kLutBGroup + j][r] = (uint8_t)best[j];
+  }
+  __syncthreads();
+  // ---- 512 pieces of 16 class bytes (16 consecutive R values of one (G, B))
+  for (int v = tid; v < 4 * kLut2B * (kLutR / 16); v += kLutThreads) {
+    const int gi = v >> 7, b = (v >> 2) & (kLut2B - 1), rq = v & 3;
+    const uint4 val = *reinterpret_cast<const uint4*>(&S.stage[gi][b][rq * 16]);
+    emit_colours(((uint32_t)(b_base + b) << 16) | ((uint32_t)(gcell * 4 + gi) << 8) | (uint32_t)(r0 + rq * 16), val);
+  }
+  // ---- 64 cells: uniform class of their 4 R x 4 G x 8 B colours, or "mixed"
+  if (tid < (kLut2B / 8) * (kLutR / 4)) {
+    const int rc = tid & (kLutR / 4 - 1), bc = tid / (kLutR / 4);
+    const uint32_t first = S.stage[0][bc * 8][rc * 4];
+    const uint32_t want = first * 0x01010101u;
+    bool same = true;
+#pragma unroll
+    for (int gi = 0; gi < 4; ++gi)
+#pragma unroll
+      for (int b = 0; b < 8; ++b)
+        same &= *reinterpret_cast<const uint32_t*>(&S.stage[gi][bc * 8 + b][rc * 4]) == want;
+    S.cells[bc][rc] = (uint8_t)(same ? first : kCellMixed);
+  }
+  __syncthreads();
+  if (tid < kLut2B / 8)
+    emit_cells(((uint32_t)(b_base / 8 + tid) << 12) | ((uint32_t)gcell << 6) | (uint32_t)(r0 >> 2),
+               *reinterpret_cast<const uint4*>(S.cells[tid]));
+}
+
 }  // namespace b200

@@ -187,9 +187,91 @@ __global__ void __launch_bounds__(kLutThreads)
   }
 }
 
+// Second form of the cooperative build: colour table AND cell table (lut_build_cells_cta),
+// every piece leaving as ONE 16-byte store per destination - or, with `mc_lut` (the NVLS
+// multicast address of the ranks' table buffers), as one multimem.st that the NVSwitch
+// replicates into all of them, so a rank's slice crosses its NVLink once instead of once
+// per peer.  Layout of a table buffer: 2^24 colour bytes, then 2^17 cell bytes.  Rank r
+// owns the B chunks r, r + world, ... (any world size up to 8).
+__device__ __forceinline__ void st_v4(uint8_t* p, const uint4& v) {
+  asm volatile("st.global.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+__device__ __forceinline__ void multimem_st_v4(uint8_t* mc, const uint4& v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(mc), "f"(__uint_as_float(v.x)),
+               "f"(__uint_as_float(v.y)), "f"(__uint_as_float(v.z)), "f"(__uint_as_float(v.w))
+               : "memory");
+}
+
+__global__ void __launch_bounds__(kLutThreads)
+    lab3_lut_build2_allgather_kernel(LutTargets tg, uint8_t* mc_lut, int nc, const double* __restrict__ params,
+                                     SymmPeers peers, int rank, int world, uint64_t epoch, int phase_mask,
+                                     unsigned long long timeout_ns) {
+  extern __shared__ __align__(16) uint8_t lut_smem_raw[];
+  Lut2Smem& S = *reinterpret_cast<Lut2Smem*>(lut_smem_raw);
+  __shared__ uint8_t* s_lut[kMaxWorld];
+  __shared__ bool is_last;
+  SymmWorkspace* me = peers.ws[rank];
+  const int tid = threadIdx.x;
+  if (phase_mask & 1) {
+    if (tid < kMaxWorld) s_lut[tid] = tid < world ? tg.lut[(rank + tid) % world] : nullptr;  // own copy first
+    __syncthreads();
+    const int rblock = blockIdx.x & 3, gcell = (blockIdx.x >> 2) & 63;
+    const int chunk = rank + world * (int)(blockIdx.x >> 8);
+    auto put = [&](size_t off, const uint4& v) {
+      if (mc_lut) {
+        multimem_st_v4(mc_lut + off, v);
+      } else {
+        for (int p = 0; p < world; ++p) st_v4(s_lut[p] + off, v);
+      }
+    };
+    lut_build_cells_cta(
+        S, nc, params, gcell, rblock * kLutR, chunk * kLut2B, [&](uint32_t id, const uint4& v) { put(id, v); },
+        [&](uint32_t idx, const uint4& v) { put((size_t(1) << 24) + idx, v); });
+    __threadfence_system();
+    __syncthreads();
+    if (tid == 0) is_last = atomicAdd(&me->lab3_lut_blocks_done, 1u) == gridDim.x - 1;
+    __syncthreads();
+    if (!is_last) return;
+    if (tid == 0) me->lab3_lut_blocks_done = 0;
+    __threadfence_system();
+    if (tid < world) signal_peer(peers, tid, rank, epoch, kFlagLab3Lut);
+  }
+  if (phase_mask & 2) {
+    if (tid < world) wait_peer(peers, rank, tid, epoch, timeout_ns, kFlagLab3Lut);
+  }
+}
+
 }  // namespace b200
 
 using namespace b200;
+
+extern "C" size_t b200_lab3_lut2_bytes(void) { return (size_t(1) << 24) + (size_t(1) << 17); }
+
+extern "C" int b200_lab3_lut_build2_allgather(void* const* lut_ptrs, void* mc_lut, int nc,
+                                              const double* params, const void* ws_ptrs, int rank,
+                                              int world, uint64_t epoch, int phase_mask,
+                                              b200_stream_t s) {
+  B200_REQUIRE(nc > 0 && nc <= kLab3C, "lab3: class count %d outside 1..%d", nc, kLab3C);
+  B200_REQUIRE(world >= 1 && world <= kMaxWorld && rank >= 0 && rank < world,
+               "lab3: bad rank/world %d/%d", rank, world);
+  B200_REQUIRE(mc_lut || lut_ptrs, "lab3: table build needs the peers' tables or their multicast address");
+  LutTargets tg;
+  for (int p = 0; p < kMaxWorld; ++p) tg.lut[p] = (lut_ptrs && p < world) ? (uint8_t*)lut_ptrs[p] : nullptr;
+  SymmPeers peers{(SymmWorkspace* const*)ws_ptrs};
+  static PerDeviceOnce attr_once;
+  if (int rc = attr_once.run("lab3_mgpu", [&]() -> int {
+        B200_CUDA_OK(cudaFuncSetAttribute(lab3_lut_build2_allgather_kernel,
+                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Lut2Smem)));
+        return 0;
+      }))
+    return rc;
+  // world <= 8 = the number of B chunks, so every rank owns at least one
+  const unsigned grid = (phase_mask & 1) ? (unsigned)lut2_chunks_of(rank, world) * 256u : 1u;
+  lab3_lut_build2_allgather_kernel<<<grid, kLutThreads, sizeof(Lut2Smem), as_stream(s)>>>(
+      tg, (uint8_t*)mc_lut, nc, params, peers, rank, world, epoch, phase_mask, kDefaultTimeoutNs);
+  B200_LAUNCH_OK();
+  return 0;
+}
 
 // Cooperative colour-table build (see kernel comment).  lut_ptrs: HOST array [world]
 // of the peer-mapped 16 MiB tables.  After the call (stream order) the local table

@@ -37,6 +37,10 @@ N.register("b200_lab3_lut_build_allgather", C.c_int,
             C.c_void_p])
 N.register("b200_lab3_apply_lut", C.c_int, [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p])
 N.register("b200_lab3_coarse_bytes", C.c_size_t, [])
+N.register("b200_lab3_lut2_bytes", C.c_size_t, [])
+N.register("b200_lab3_lut_build2_allgather", C.c_int,
+           [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_uint64, C.c_int, C.c_void_p])
+N.register("b200_lab3_apply_lut2", C.c_int, [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p])
 N.register("b200_sort_mgpu_splitters", C.c_int,
            [C.c_void_p, C.c_size_t, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_uint64, C.c_int,
             C.c_void_p])
@@ -221,6 +225,23 @@ def apply_lut(img: torch.Tensor, lut_addr: int, coarse: Optional[torch.Tensor] =
     return img
 
 
+def lut_build2_allgather(lut_ptrs: Optional[Sequence[int]], mc_lut: int, nc: int, params: torch.Tensor,
+                         ws_ptrs_dev: torch.Tensor, rank: int, world: int, epoch: int, phase_mask: int = 3) -> None:
+    """Colour table + cell table built cooperatively, 16-byte stores: into every peer's buffer
+    (``lut_ptrs``), or one multimem.st per piece on the multicast address ``mc_lut``."""
+    arr = _ptr_array(lut_ptrs) if lut_ptrs is not None else None
+    N.check(N.lib().b200_lab3_lut_build2_allgather(arr, C.c_void_p(mc_lut or 0), nc, N.ptr(params),
+                                                   N.ptr(ws_ptrs_dev), rank, world, epoch, phase_mask,
+                                                   N.current_stream_ptr()), "b200_lab3_lut_build2_allgather")
+
+
+def apply_lut2(img: torch.Tensor, lut_addr: int) -> torch.Tensor:
+    """Image pass against a table buffer that carries its cell table (b200_lab3_lut2_bytes())."""
+    N.check(N.lib().b200_lab3_apply_lut2(N.ptr(img), img.shape[0] * img.shape[1], C.c_void_p(lut_addr),
+                                         N.current_stream_ptr()), "b200_lab3_apply_lut2")
+    return img
+
+
 class ShardedClassifier:
     """Row-sharded lab3: global sample points, statistics all-reduced, local classify.
     With the fused implementation on several GPUs the 2^24-entry colour table is built
@@ -231,20 +252,35 @@ class ShardedClassifier:
 
     def __init__(self, group: PeerGroup, w: int, h_total: int, classes, impl: str = "fused",
                  variant: str = "auto"):
-        # impl "nvls": as "fused", but the statistics are all-reduced by the NVSwitch
-        # (multimem.red on the multicast address of a parallel/vmm.py buffer)
-        assert impl in ("fused", "nccl", "nvls")
-        self.nvls = impl == "nvls"
-        self._acc_buf = None
-        if self.nvls:
+        # impl: "fused" = product path: in-kernel all-reduce and cooperative table build over peer
+        #         memory, through the NVSwitch (multimem.red / multimem.st on multicast buffers of
+        #         parallel/vmm.py) when the system has NVLS, else with peer stores;
+        #       "nvls"  = as "fused" but NVLS is required (raises without it);
+        #       "p2p"   = as "fused" but never multicast (B200LABS_NVLS=0 does the same);
+        #       "nccl"  = baseline: library all-reduce, every rank builds the whole table.
+        import os
+        assert impl in ("fused", "nccl", "nvls", "p2p")
+        self.nvls = False
+        self._acc_buf = self._lut_buf = None
+        want_mc = (impl in ("fused", "nvls") and group.world > 1 and
+                   (impl == "nvls" or os.environ.get("B200LABS_NVLS", "1") != "0"))
+        if want_mc:
             from . import vmm
-            impl = "fused"
-            self._acc_buf = vmm.alloc(group, 2 * 32 * 10 * 8, multicast=True, map_peers=False)
-            if not self._acc_buf.mc_ptr:
+            try:
+                self._acc_buf = vmm.alloc(group, 2 * 32 * 10 * 8, multicast=True, map_peers=False)
+            except RuntimeError:
+                self._acc_buf = None
+            if self._acc_buf is not None and not self._acc_buf.mc_ptr:
                 self._acc_buf.free()
-                raise RuntimeError("NVLS multicast is not available on this system")
-            self._acc = self._acc_buf.view(torch.int64, 2 * 32 * 10)
-            self._nvls_calls = 0
+                self._acc_buf = None
+            self.nvls = self._acc_buf is not None
+            if self.nvls:
+                self._acc = self._acc_buf.view(torch.int64, 2 * 32 * 10)
+                self._nvls_calls = 0
+        if impl == "nvls" and not self.nvls:
+            raise RuntimeError("NVLS multicast is not available on this system")
+        if impl in ("nvls", "p2p"):
+            impl = "fused"
         self.group, self.w, self.h_total, self.impl, self.variant = group, w, h_total, impl, variant
         self.y0, self.y1 = shard_rows(h_total, group.world)[group.rank]
         self.h_local = self.y1 - self.y0
@@ -261,13 +297,20 @@ class ShardedClassifier:
         self.scratch = torch.empty(need, dtype=torch.uint8, device=dev) if need else None
         self.ws = group.workspace()
         lut = need > 0
-        self.coop_lut = lut and impl == "fused" and group.world > 1 and group.world & (group.world - 1) == 0
-        self.sym_lut = group.alloc(1 << 24) if self.coop_lut else None
-        self.coarse = (torch.empty(int(N.lib().b200_lab3_coarse_bytes()), dtype=torch.uint8, device=dev)
-                       if self.coop_lut else None)
-        # kernels per step: stats(1) [+ finalize for nccl] + classify (lut: build + cell table + apply)
-        two_level = lut and npix >= (1 << 22)
-        self.launches_per_step = (1 if impl == "fused" else 2) + ((3 if two_level else 2) if lut else 1)
+        # cooperative table build: any world size; the table buffer carries its cell table
+        self.coop_lut = lut and impl == "fused" and group.world > 1
+        self.sym_lut, self._lut_mc, self._lut_local = None, 0, 0
+        if self.coop_lut:
+            lut_bytes = int(N.lib().b200_lab3_lut2_bytes())
+            if self.nvls:
+                from . import vmm
+                self._lut_buf = vmm.alloc(group, lut_bytes, multicast=True, map_peers=False)
+                self._lut_mc, self._lut_local = self._lut_buf.mc_ptr, self._lut_buf.local_ptr
+            if not self._lut_mc:
+                self.sym_lut = group.alloc(lut_bytes)
+                self._lut_local = self.sym_lut.local_ptr
+        # kernels per step: stats(1) [+ finalize for nccl] + classify (lut: build [+ cells] + apply)
+        self.launches_per_step = (1 if impl == "fused" else 2) + (2 if lut else 1)
 
     def fit(self) -> torch.Tensor:
         g = self.group
@@ -292,15 +335,18 @@ class ShardedClassifier:
         self.fit()
         if self.coop_lut:
             g = self.group
-            lut_build_allgather(self.sym_lut.peer_ptrs, self.nc, self.params, self.ws.ptrs_dev, g.rank,
-                                g.world, g.next_epoch(), 3)
-            return apply_lut(self.band, self.sym_lut.local_ptr, self.coarse)
+            lut_build2_allgather(self.sym_lut.peer_ptrs if self.sym_lut is not None else None, self._lut_mc,
+                                 self.nc, self.params, self.ws.ptrs_dev, g.rank, g.world, g.next_epoch(), 3)
+            return apply_lut2(self.band, self._lut_local)
         return CL.lab3_classify(self.band, self.params, variant=self.variant, scratch=self.scratch)
 
     def free(self) -> None:
         if self.sym_lut is not None:
             self.sym_lut.free()
             self.sym_lut = None
+        if self._lut_buf is not None:
+            self._lut_buf.free()
+            self._lut_buf = None
         if self._acc_buf is not None:
             self._acc = None
             self._acc_buf.free()

@@ -230,6 +230,17 @@ int b200_lab3_lut_build_allgather(void* const* lut_ptrs, int nc, const double* p
 int b200_lab3_apply_lut(void* img, int64_t npix, const void* lut, void* coarse_scratch,
                         b200_stream_t s);
 size_t b200_lab3_coarse_bytes(void);
+/* Second form of the cooperative build: colour table AND cell table from one kernel, every
+ * piece leaving as a 16-byte store.  A table buffer is b200_lab3_lut2_bytes() long (2^24
+ * colour bytes, then 2^17 cell bytes).  lut_ptrs: HOST array [world] of the peer-mapped
+ * buffers; mc_lut (may be NULL): NVLS multicast address of the same buffers - when given,
+ * each piece is ONE multimem.st that the NVSwitch replicates to every GPU.  Any world <= 8.
+ * Follow with b200_lab3_apply_lut2 on the local buffer.  (No counterpart in the reference.) */
+size_t b200_lab3_lut2_bytes(void);
+int b200_lab3_lut_build2_allgather(void* const* lut_ptrs, void* mc_lut, int nc, const double* params,
+                                   const void* ws_ptrs, int rank, int world, uint64_t epoch,
+                                   int phase_mask, b200_stream_t s);
+int b200_lab3_apply_lut2(void* img, int64_t npix, const void* lut_and_cells, b200_stream_t s);
 
 /* lab5 fused sample sort, step 1: sample + exchange + splitters (one CTA). */
 int b200_sort_mgpu_splitters(const void* keys, size_t n_local, int key_type,

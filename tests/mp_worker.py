@@ -95,7 +95,8 @@ def main():
     classes = [np.stack([rng.integers(0, w, 500), rng.integers(0, h, 500)], axis=1) for _ in range(nc)]
     p_want = MahalanobisClassifier.reference_params(img, classes, mode="moments")
     c_want = MahalanobisClassifier.reference_classify(img, p_want)
-    for impl, variant in (("fused", "auto"), ("nccl", "auto"), ("fused", "lut"), ("nccl", "lut"), ("nvls", "lut")):
+    for impl, variant in (("fused", "auto"), ("nccl", "auto"), ("fused", "lut"), ("p2p", "lut"), ("nccl", "lut"),
+                          ("nvls", "lut")):
         try:
             m = ShardedClassifier(g, w, h, classes, impl=impl, variant=variant)
         except RuntimeError as exc:                      # NVLS needs NVSwitch multicast
@@ -104,7 +105,8 @@ def main():
             if rank == 0:
                 print("NVLS path skipped:", type(exc).__name__, exc)
             continue
-        assert m.coop_lut == (impl in ("fused", "nvls") and variant == "lut")
+        assert m.coop_lut == (impl in ("fused", "nvls", "p2p") and variant == "lut")
+        assert not (impl == "p2p" and m.nvls)
         for rep in range(3):
             m.band.copy_(torch.from_numpy(img[m.y0:m.y1].copy()).view(torch.int32).reshape(m.h_local, w))
             g.barrier()

@@ -99,6 +99,52 @@ def test_lab3_cooperative_lut_matches_oracle(cuda_device, world):
         b.free()
 
 
+@pytest.mark.parametrize("world", [1, 2, 3, 8])
+def test_lab3_cooperative_table_with_cells_matches_oracle(cuda_device, world):
+    """Second form of the cooperative build (colour table + cell table from one kernel, 16-byte
+    stores, any world size): every rank's buffer ends up identical, the colour bytes equal the
+    first form's table, the cell bytes equal what the separate coarsening pass derives, and the
+    image pass on top of it matches the CPU classifier."""
+    rng = np.random.default_rng(90 + world)
+    h, w, nc = 96, 128, 32
+    img = rng.integers(0, 256, size=(h, w, 4), dtype=np.uint8)
+    classes = [np.stack([rng.integers(0, w, 200), rng.integers(0, h, 200)], axis=1) for _ in range(nc)]
+    params = MahalanobisClassifier.reference_params(img, classes, mode="moments")
+    want = MahalanobisClassifier.reference_classify(img, params)
+    d_params = torch.from_numpy(params).to(cuda_device)
+    group = LocalPeerGroup(world, cuda_device)
+    ws = group.workspaces()
+    nbytes = int(N.lib().b200_lab3_lut2_bytes())
+    luts = group.alloc(nbytes)
+    for rep in range(2):                       # second round: stale bytes of round one are overwritten
+        epoch = group.next_epoch()
+        for phase in (1, 2):
+            for r in range(world):
+                S.lut_build2_allgather(luts[r].peer_ptrs, 0, nc, d_params, ws[r].ptrs_dev, r, world, epoch, phase)
+    torch.cuda.synchronize()
+    for r in range(1, world):
+        assert torch.equal(luts[0].local[:nbytes], luts[r].local[:nbytes]), r
+    # reference table: the single-GPU older build + separate coarsening pass
+    solo = LocalPeerGroup(1, cuda_device)
+    old = solo.alloc(1 << 24)
+    S.lut_build_allgather(old[0].peer_ptrs, nc, d_params, solo.workspaces()[0].ptrs_dev, 0, 1, solo.next_epoch(), 3)
+    assert torch.equal(luts[0].local[: 1 << 24], old[0].local[: 1 << 24])
+    big = torch.randint(-2 ** 31, 2 ** 31 - 1, (2048, 2304), dtype=torch.int32, device=cuda_device)
+    coarse = torch.empty(int(N.lib().b200_lab3_coarse_bytes()), dtype=torch.uint8, device=cuda_device)
+    one, two = big.clone(), big.clone()
+    S.apply_lut(one, old[0].local_ptr, coarse)                 # derives `coarse` from the old table
+    S.apply_lut2(two, luts[world - 1].local_ptr)
+    torch.cuda.synchronize()
+    assert torch.equal(coarse, luts[0].local[1 << 24: nbytes])
+    assert torch.equal(one, two)
+    for r, (a, b) in enumerate(shard_rows(h, world)):
+        d = torch.from_numpy(img[a:b].copy()).to(cuda_device)
+        S.apply_lut2(d, luts[r].local_ptr)
+        assert np.array_equal(d.cpu().numpy(), want[a:b]), r
+    for b in luts + old:
+        b.free()
+
+
 @pytest.mark.parametrize("world", [2, 3, 4, 6, 8])
 @pytest.mark.parametrize("dtype,kind", [(np.int32, "random"), (np.float32, "random"), (np.int32, "dups"),
                                         (np.int32, "equal"), (np.uint32, "skewed")])
