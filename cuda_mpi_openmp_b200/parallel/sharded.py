@@ -538,4 +538,5 @@ class ShardedSort:
         return self._count_host
 
     def result(self) -> torch.Tensor:
-        return self.bucket[: self.count()]
+        n = self.count()          # may re-allocate `bucket` (overflow retry): read it only afterwards
+        return self.bucket[:n]

@@ -69,12 +69,19 @@ class SymmetricBuffer:
         return _wrap(self.peer_ptrs[r] + byte_offset, nbytes, self.group.device).view(dtype)
 
     def free(self):
+        """Collective over the group: every rank first closes its mappings of the peers' memory,
+        then - after a barrier - releases its own.  (Freeing memory that a peer still has mapped,
+        and then handing out the same address again, is how a re-allocation right after a free
+        came back with `invalid argument`.)"""
         L = N.lib()
+        had_peers = bool(self._opened)
         for p in self._opened:
-            L.b200_ipc_close(C.c_void_p(p))
+            N.check(L.b200_ipc_close(C.c_void_p(p)), "b200_ipc_close")
         self._opened = []
+        if had_peers or getattr(self.group, "world", 1) > 1:
+            self.group.barrier()
         if self.local_ptr:
-            L.b200_dev_free(C.c_void_p(self.local_ptr))
+            N.check(L.b200_dev_free(C.c_void_p(self.local_ptr)), "b200_dev_free")
             self.local_ptr = 0
 
 

@@ -22,4 +22,8 @@ def test_sharded_labs_over_all_visible_gpus(built, cuda_device):
            "--master-addr", "127.0.0.1", "--master-port", "29533", str(built / "tests/mp_worker.py")]
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=900, cwd=built,
                        env={**os.environ, "NCCL_DEBUG": "WARN"})
+    log_dir = built / "gpurun_out"                  # full worker output survives the GPU call
+    log_dir.mkdir(exist_ok=True)
+    (log_dir / "mp_worker_stdout.log").write_text(r.stdout)
+    (log_dir / "mp_worker_stderr.log").write_text(r.stderr)
     assert r.returncode == 0 and "MP_WORKER_OK" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
