@@ -35,7 +35,7 @@ CPU_BINS  := lab1/src/cpu_exe lab1/src/cpu_exe_to_plot lab2/src/cpu_exe lab3/src
 # the binaries' directories hold nothing that is tracked, so a fresh checkout lacks them
 $(shell mkdir -p lab1/src lab2/src lab3/src lab5/src hw1/src hw2/src gpu_info/src)
 
-.PHONY: all lib bins cpu clean sass
+.PHONY: all lib bins cpu clean sass yardsticks
 all: lib bins
 lib: $(SO) $(AR_LIB)
 bins: $(CUDA_BINS) $(CPU_BINS)
@@ -105,6 +105,11 @@ hw1/src/hw1: apps/hw1.c
 	$(CC) $(CFLAGS) $< -lm -o $@
 hw2/src/hw2: apps/hw2.c
 	$(CC) $(CFLAGS) $< -o $@
+
+# Yardsticks and reference drivers (measurement only; nothing here is linked into the library)
+yardsticks: | $(BUILD)
+	$(NVCC) -O3 -std=c++17 -arch=sm_100a -o $(BUILD)/sort_yardstick tools/sort_yardstick.cu
+	bash baseline/build_lab1_driver.sh
 
 # SASS listings for profiles/ (evidence of UTMALDG/UTMASTG, vector widths, ...)
 sass: $(SO)

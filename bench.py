@@ -49,6 +49,9 @@ def parse_args():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-extras", action="store_true")
     ap.add_argument("--e2e-steps", type=int, default=None)
+    ap.add_argument("--ref-shape", default="stock",
+                    help="reference arm: 'stock' = its fixed block 32x32 / grid 16x16; 'best' = the fastest "
+                         "shape of tools/reference_sweep.py (profiles/reference_sweep.json); or 'bx,by,gx,gy'")
     ap.add_argument("--ref-max-seconds", type=float, default=420.0,
                     help="reference arm: cap on total wall time; steps are reduced (and reported) to fit")
     return ap.parse_args()
@@ -489,7 +492,17 @@ def run_reference(args):
     in_path, out_path = shm / f"b200ref_in_{rank}.data", shm / f"b200ref_out_{rank}.data"
     write_synthetic_image(in_path, w, rows_per_chunk, seed=1234 + rank)
     env = {**os.environ, "CUDA_VISIBLE_DEVICES": str(local_rank)}
-    stdin = f"32\n32\n16\n16\n{in_path}\n{out_path}\n"
+    shape = (32, 32, 16, 16)
+    if args.ref_shape == "best":
+        try:
+            sweep = json.loads((ROOT / "profiles" / "reference_sweep.json").read_text())
+            best = next(v for k, v in sweep.items() if k.startswith("65536"))["reference_best_shape"]
+            shape = (*best["block"], *best["grid"])
+        except Exception:  # noqa: BLE001 - no sweep on record: stay with the stock shape
+            args.ref_shape = "stock"
+    elif args.ref_shape != "stock":
+        shape = tuple(int(v) for v in args.ref_shape.split(","))
+    stdin = "%d\n%d\n%d\n%d\n" % shape + f"{in_path}\n{out_path}\n"
 
     def one_step():
         return binary_step(exe, stdin, env, n_chunks)
@@ -540,7 +553,9 @@ def run_reference(args):
                                     "nvcc -arch=sm_100a)", "image": f"{w}x{h}", "global_batch": 1, "seq_len": w * h,
                            "parallelism": f"{world} independent processes, one band each, no halo exchange "
                                           "(the reference has no multi-GPU code)",
-                           "launch": "block 32x32, grid 16x16 (the reference's own fixed shape)",
+                           "launch": "block %dx%d, grid %dx%d (%s)" % (*shape, "the reference's own fixed shape"
+                                                                       if args.ref_shape == "stock" else
+                                                                       "--ref-shape " + args.ref_shape),
                            "chunks_per_rank": n_chunks, "rows_per_chunk": rows_per_chunk,
                            "note": "device ms = the binary's own cudaEvent kernel time summed over chunks; "
                                    "chunking needed because the reference indexes pixels with int"},
