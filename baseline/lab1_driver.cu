@@ -8,6 +8,7 @@
 // is included below.  Launch shapes: the reference's own <<<512,512>>> and a sweep.
 // Output: one JSON object on stdout.
 #include <cuda_runtime.h>
+#include <dlfcn.h>
 
 #include <algorithm>
 #include <cstdio>
@@ -81,10 +82,37 @@ int main(int argc, char** argv) {
       first = false;
       if (ms < best) best = ms, bg = g, bb = bl;
     }
+  // the same loop, same events, around this repository's kernel (library path in argv[2])
+  float own_ms = -1.f;
+  if (argc > 2) {
+    typedef int (*vecsub_fn)(const double*, const double*, double*, size_t, void*);
+    void* lib = dlopen(argv[2], RTLD_NOW);
+    vecsub_fn fn = lib ? (vecsub_fn)dlsym(lib, "b200_vecsub_f64") : nullptr;
+    if (fn) {
+      cudaEvent_t e0, e1;
+      CK(cudaEventCreate(&e0));
+      CK(cudaEventCreate(&e1));
+      std::vector<float> t;
+      for (int it = 0; it < 13; ++it) {
+        CK(cudaEventRecord(e0));
+        if (fn(a, b, c, (size_t)n, nullptr) != 0) break;
+        CK(cudaEventRecord(e1));
+        CK(cudaEventSynchronize(e1));
+        float ms;
+        CK(cudaEventElapsedTime(&ms, e0, e1));
+        if (it >= 3) t.push_back(ms);
+      }
+      if (t.size() == 10) {
+        std::sort(t.begin(), t.end());
+        own_ms = t[5];
+      }
+    }
+  }
   check<<<1184, 256>>>(a, b, c, n, bad);
   int h_bad = 0;
   CK(cudaMemcpy(&h_bad, bad, 4, cudaMemcpyDeviceToHost));
-  printf("], \"best\": {\"grid\": %d, \"block\": %d, \"ms\": %.5f, \"GBps\": %.1f}, \"wrong_elements\": %d}\n", bg, bb,
-         best, 24.0 * n / best / 1e6, h_bad);
+  printf("], \"best\": {\"grid\": %d, \"block\": %d, \"ms\": %.5f, \"GBps\": %.1f}, \"this_build_same_loop\": "
+         "{\"ms\": %.5f, \"GBps\": %.1f}, \"wrong_elements\": %d}\n",
+         bg, bb, best, 24.0 * n / best / 1e6, own_ms, own_ms > 0 ? 24.0 * n / own_ms / 1e6 : 0.0, h_bad);
   return h_bad != 0;
 }
