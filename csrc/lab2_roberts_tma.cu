@@ -27,20 +27,38 @@
 
 namespace b200 {
 
+// Tile shape knobs.  Measured on B200 (GB/s at 65536^2 / 16384^2): the default 32-row tiles,
+// 4-row warp blocks, 4 stages, 2 staging blocks 5867 / 6632; 64-row tiles with 8-row blocks
+// (less halo, less repeated luminance), 2 stages, 1 staging block 5566 / 5492; 32-row tiles
+// with 8-row blocks (8 consumer warps) 5444 / 6003; 48-row tiles, 8-row blocks, 3 stages
+// 5486 / 5426.  Fewer, fatter warps lose more to latency than they save in instructions.
+#ifndef B200_TMA_TILE_H
+#define B200_TMA_TILE_H 32
+#endif
+#ifndef B200_TMA_SUB_H
+#define B200_TMA_SUB_H 4
+#endif
+#ifndef B200_TMA_STAGES
+#define B200_TMA_STAGES 4
+#endif
+#ifndef B200_TMA_OUTBUFS
+#define B200_TMA_OUTBUFS 2
+#endif
 constexpr int kTileW = 256;               // output px per tile row
-constexpr int kTileH = 32;                // output rows per tile
+constexpr int kTileH = B200_TMA_TILE_H;   // output rows per tile
 constexpr int kBoxW = kTileW + 4;         // loaded px per row (260 -> 130 u64)
 constexpr int kBoxH = kTileH + 1;         // loaded rows
 constexpr int kPitch = kBoxW * 4;         // 1040 B, 16-byte multiple
 constexpr int kStageBytes = kPitch * kBoxH;  // 34320
-constexpr int kStageStride = 34816;       // 128-byte aligned slot
-constexpr int kStages = 4;
-constexpr int kConsumerWarps = 16;        // 2 column halves x 8 row groups of 4
-constexpr int kSubW = 128, kSubH = 4;     // per-warp output block
+constexpr int kStageStride = (kStageBytes + 127) / 128 * 128;  // 128-byte aligned slot
+constexpr int kStages = B200_TMA_STAGES;
+constexpr int kSubW = 128, kSubH = B200_TMA_SUB_H;  // per-warp output block
+constexpr int kConsumerWarps = 2 * (kTileH / kSubH);  // 2 column halves x row groups of kSubH
+constexpr int kOutBufs = B200_TMA_OUTBUFS;  // staging blocks per warp handed to the TMA store in turn
 constexpr int kOutBytes = kSubW * 4 * kSubH;  // 2048
 constexpr int kTmaThreads = (kConsumerWarps + 1) * 32;
 constexpr int kSmemBytes =
-    kStages * kStageStride + kConsumerWarps * 2 * kOutBytes + 2 * kStages * 8 + 128;
+    kStages * kStageStride + kConsumerWarps * kOutBufs * kOutBytes + 2 * kStages * 8 + 128;
 
 struct TmaParams {
   const uint32_t* below;  // row after the band (maybe on a peer GPU), never null
@@ -58,7 +76,7 @@ __global__ void __launch_bounds__(kTmaThreads, 1)
   extern __shared__ __align__(128) uint8_t smem[];
   uint8_t* in_tiles = smem;
   uint8_t* out_stage = smem + kStages * kStageStride;
-  uint64_t* full = (uint64_t*)(out_stage + kConsumerWarps * 2 * kOutBytes);
+  uint64_t* full = (uint64_t*)(out_stage + kConsumerWarps * kOutBufs * kOutBytes);
   uint64_t* empty = full + kStages;
 
   const int warp = threadIdx.x >> 5;
@@ -115,7 +133,7 @@ __global__ void __launch_bounds__(kTmaThreads, 1)
   prefetch_tmap(&out_map);
   const int chalf = warp & 1;       // which 128-px half of the tile
   const int rgrp = warp >> 1;       // rows rgrp*4 .. rgrp*4+3
-  uint8_t* my_out = out_stage + warp * 2 * kOutBytes;
+  uint8_t* my_out = out_stage + warp * kOutBufs * kOutBytes;
   int it = 0;
   // The staging half is picked by the number of stores this warp has ISSUED, not by the
   // tile counter: a warp skips tiles whose block lies outside the image without storing,
@@ -170,10 +188,10 @@ __global__ void __launch_bounds__(kTmaThreads, 1)
     __syncwarp();
     if (lane == 0) mbar_arrive(&empty[s]);
 
-    // staging buffer (n_stores & 1) was handed to the TMA store two stores ago
-    if (lane == 0) tma_store_wait_read<1>();
+    // this staging block was handed to the TMA store kOutBufs stores ago
+    if (lane == 0) tma_store_wait_read<kOutBufs - 1>();
     __syncwarp();
-    uint4* ob = (uint4*)(my_out + (n_stores & 1) * kOutBytes) + lane;
+    uint4* ob = (uint4*)(my_out + (n_stores % kOutBufs) * kOutBytes) + lane;
 
     float c0 = luma_rgba(px[0].x), c1 = luma_rgba(px[0].y), c2 = luma_rgba(px[0].z),
           c3 = luma_rgba(px[0].w);
@@ -198,7 +216,7 @@ __global__ void __launch_bounds__(kTmaThreads, 1)
     fence_proxy_async_smem();  // generic-proxy writes -> visible to the TMA engine
     __syncwarp();
     if (lane == 0) {
-      tma_store_2d(&out_map, my_out + (n_stores & 1) * kOutBytes, tx * kTileW + chalf * kSubW, (int)y0);
+      tma_store_2d(&out_map, my_out + (n_stores % kOutBufs) * kOutBytes, tx * kTileW + chalf * kSubW, (int)y0);
       tma_store_commit();
     }
     ++n_stores;
