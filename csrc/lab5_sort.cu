@@ -88,6 +88,59 @@ __global__ void __launch_bounds__(kHistThreads)
   }
 }
 
+// Same histograms for large arrays, with counters laid out so that the atomics of a warp never
+// share a bank: counter (digit position p, bin b, lane l) lives at word (p * 256 + b) * 32 + l,
+// i.e. every lane owns one bank column.  A warp-wide shared-memory atomic indexed by 32 random
+// digits costs ~5 wavefronts of the L1 data pipe (bank conflicts), which made the kernel above
+// pipe-bound at 113 us for 2^26 keys (profiles/ncu_prof_lab5_v5a.md: 92% of the pipe); here it
+// costs one.  128 KB of counters, one 1024-thread CTA per SM.
+constexpr int kHist2Threads = 1024;
+constexpr int kHist2Smem = 4 * kRadix * 32 * 4;  // 131072 bytes
+template <int KT>
+__global__ void __launch_bounds__(kHist2Threads, 1)
+    sort_hist_lanes_kernel(const uint32_t* __restrict__ keys, size_t n,
+                           const unsigned long long* __restrict__ n_dev,
+                           unsigned long long* __restrict__ hist /* [4][256] */) {
+  if (n_dev) n = (size_t)*n_dev;
+  extern __shared__ __align__(16) uint8_t hist_smem_raw[];
+  uint32_t* cnt = reinterpret_cast<uint32_t*>(hist_smem_raw);  // [4][256][32]
+  const int tid = threadIdx.x, lane = tid & 31;
+  for (int i = tid; i < kHist2Smem / 16; i += kHist2Threads) reinterpret_cast<uint4*>(cnt)[i] = make_uint4(0, 0, 0, 0);
+  __syncthreads();
+  const uint32_t base = smem_u32(cnt) + 4u * lane;
+  auto add = [&](uint32_t k) {
+    const uint32_t o = to_ordered<KT>(k);
+    // address = base + (p * 256 + byte p of o) * 128
+    asm volatile(
+        "{\n\t.reg .b32 d, a;\n\t"
+        "prmt.b32 d, %0, 0, 0x4440;\n\t mad.lo.u32 a, d, 128, %1;\n\t red.shared.add.u32 [a], 1;\n\t"
+        "prmt.b32 d, %0, 0, 0x4441;\n\t mad.lo.u32 a, d, 128, %1;\n\t red.shared.add.u32 [a+32768], 1;\n\t"
+        "prmt.b32 d, %0, 0, 0x4442;\n\t mad.lo.u32 a, d, 128, %1;\n\t red.shared.add.u32 [a+65536], 1;\n\t"
+        "prmt.b32 d, %0, 0, 0x4443;\n\t mad.lo.u32 a, d, 128, %1;\n\t red.shared.add.u32 [a+98304], 1;\n\t}" ::"r"(o),
+        "r"(base)
+        : "memory");
+  };
+  const size_t n_vec = (((uintptr_t)keys) & 15u) == 0 ? n / 4 : 0;
+  const size_t stride = (size_t)gridDim.x * kHist2Threads;
+  size_t i = (size_t)blockIdx.x * kHist2Threads + tid;
+  for (; i + stride < n_vec; i += 2 * stride) {  // two loads in flight per thread
+    const uint4 v = ld_stream_u4(keys + 4 * i), w = ld_stream_u4(keys + 4 * (i + stride));
+    add(v.x), add(v.y), add(v.z), add(v.w), add(w.x), add(w.y), add(w.z), add(w.w);
+  }
+  for (; i < n_vec; i += stride) {
+    const uint4 v = ld_stream_u4(keys + 4 * i);
+    add(v.x), add(v.y), add(v.z), add(v.w);
+  }
+  for (size_t j = n_vec * 4 + (size_t)blockIdx.x * kHist2Threads + tid; j < n; j += stride) add(keys[j]);
+  __syncthreads();
+  // thread t sums the 32 lane columns of counter row t, starting at its own column so that the
+  // lanes of a warp (consecutive rows) read 32 different banks
+  unsigned long long sum = 0;
+#pragma unroll 8
+  for (int j = 0; j < 32; ++j) sum += cnt[tid * 32 + ((j + lane) & 31)];
+  if (sum) atomicAdd(hist + tid, sum);
+}
+
 // exclusive scan of each 256-bin histogram, in place: hist[p][d] -> first output
 // index of digit d in pass p
 __global__ void sort_scan_kernel(unsigned long long* __restrict__ hist, int passes) {
@@ -113,7 +166,7 @@ __global__ void sort_scan_kernel(unsigned long long* __restrict__ hist, int pass
 constexpr unsigned long long kStatusShift = 62, kPassShift = 58;
 constexpr unsigned long long kValueMask = (1ull << kPassShift) - 1;
 constexpr unsigned long long kStAggregate = 1, kStInclusive = 2;
-constexpr int kGroupTiles = 16;  // look-back groups: [tiles][256] entries, then [groups][256]
+constexpr int kGroupTiles = 16;  // look-back groups: [tiles][256] entries, then [groups][256] twice
 
 __device__ __forceinline__ unsigned long long ld_lookback(const unsigned long long* p) {
   unsigned long long v;
@@ -134,8 +187,9 @@ __device__ __forceinline__ void st_lookback(unsigned long long* p, unsigned long
 //     shared word per (warp, digit) - low half = lane mask of the current row (atomicOr),
 //     high half = next free tile position - read with one LDS.64 and rewritten by the
 //     group's highest lane with one STS.64 (which also clears the mask for the next row);
-//   * the FIRST pass has no earlier order to keep: it counts on CTA-wide counters, turns
-//     them into cursors and places every key with one atomicAdd on its digit's cursor;
+//   * the FIRST pass has no earlier order to keep: it counts on CTA-wide counters (one bank
+//     column per lane: conflict-free), turns them into cursors and places every key with one
+//     atomicAdd on its (digit, lane) cursor;
 //   * keys kept in their ordered (unsigned-comparable) form between passes: the first
 //     pass converts on load, the last one converts back on store, the two in the middle
 //     extract a digit with a single byte-permute;
@@ -179,16 +233,17 @@ __device__ __forceinline__ void count_digit(uint32_t key, uint32_t sel, uint32_t
       "red.shared.add.u32 [a+%4], 1;\n\t}" ::"r"(key), "r"(sel), "r"(table_smem), "n"(STRIDE), "n"(STRIDE - 4)
       : "memory");
 }
-// position = cursor[digit(key)]++ on a table of 4-byte entries
+// position = cursor[digit(key)]++ on a table of STRIDE-byte entries
+template <int STRIDE>
 __device__ __forceinline__ uint32_t take_slot(uint32_t key, uint32_t sel, uint32_t table_smem) {
   uint32_t r;
   asm volatile(
       "{\n\t.reg .b32 d, a;\n\t"
       "prmt.b32 d, %1, 0, %2;\n\t"
-      "mad.lo.u32 a, d, 4, %3;\n\t"
+      "mad.lo.u32 a, d, %4, %3;\n\t"
       "atom.shared.add.u32 %0, [a], 1;\n\t}"
       : "=r"(r)
-      : "r"(key), "r"(sel), "r"(table_smem)
+      : "r"(key), "r"(sel), "r"(table_smem), "n"(STRIDE)
       : "memory");
   return r;
 }
@@ -211,7 +266,9 @@ __device__ __forceinline__ void pass_tile(PassSmemT<WIDE>& S, const uint32_t* __
   const uint32_t sel = 0x4440u | (uint32_t)pass;  // byte `pass` of the key -> bits 0..7
   const uint32_t w_off = warp * (kItems * 32) + lane;
   unsigned long long* pr = S.pair[warp];
-  // first pass: one counter per digit for the whole CTA (S.pair[0] reused as 256 words)
+  // first pass: CTA-wide counters, one bank column per lane - counter (digit d, lane l) is word
+  // d * 32 + l of the 32 KB that the other passes use for their per-warp pairs - so a warp's
+  // atomics never conflict (a warp access indexed by 32 random digits costs ~5 wavefronts)
   uint32_t* cta_cnt = reinterpret_cast<uint32_t*>(&S.pair[0][0]);
 
   // ---- load (warp-striped: logical order == memory order) + early count
@@ -223,11 +280,12 @@ __device__ __forceinline__ void pass_tile(PassSmemT<WIDE>& S, const uint32_t* __
     if (FIRST) k = to_ordered<KT>(k);
     key[i] = k;
   }
-  const uint32_t tbl = FIRST ? smem_u32(cta_cnt) : smem_u32(pr);
+  // count_digit adds STRIDE - 4 to the entry address: bias the lane-column table accordingly
+  const uint32_t tbl = FIRST ? smem_u32(cta_cnt) + 4u * lane : smem_u32(pr);
 #pragma unroll
   for (int i = 0; i < kItems; ++i)
     if (FULL || (w_off + i * 32) < n_valid) {
-      if (FIRST) count_digit<4>(key[i], sel, tbl);
+      if (FIRST) count_digit<128>(key[i], sel, tbl - 124u);
       else count_digit<8>(key[i], sel, tbl);
     }
   __syncthreads();
@@ -237,13 +295,15 @@ __device__ __forceinline__ void pass_tile(PassSmemT<WIDE>& S, const uint32_t* __
   const unsigned long long tag = ((unsigned long long)pass << kPassShift);
   if (tid < kRadix) {
     uint32_t* col = reinterpret_cast<uint32_t*>(&S.pair[0][tid]) + 1;
-    if (FIRST) {
-      count = cta_cnt[tid];
+    if (FIRST) {  // my row of 32 lane columns, walked from column `lane` on: 32 different banks per warp
+#pragma unroll 8
+      for (int j = 0; j < 32; ++j) count += cta_cnt[tid * 32 + ((j + lane) & 31)];
     } else {
 #pragma unroll
       for (int wv = 0; wv < kSortWarps; ++wv) count += col[wv * kRadix * 2];
     }
-    st_lookback(lookback + (size_t)tile * kRadix + tid, (kStAggregate << kStatusShift) | tag | count);
+    if (!FIRST)  // successors look back at this (the first pass reserves with atomics instead)
+      st_lookback(lookback + (size_t)tile * kRadix + tid, (kStAggregate << kStatusShift) | tag | count);
     uint32_t inc = count;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
@@ -255,8 +315,15 @@ __device__ __forceinline__ void pass_tile(PassSmemT<WIDE>& S, const uint32_t* __
     uint32_t base = 0;
     for (int wv = 0; wv < warp; ++wv) base += S.scan_tmp[wv];
     start = base + inc - count;
-    if (FIRST) {
-      cta_cnt[tid] = start;  // from count to cursor: the next free tile position of the digit
+    if (FIRST) {  // counts -> cursors: each lane column gets its own sub-range of the digit's run
+      uint32_t run = start;
+#pragma unroll 8
+      for (int j = 0; j < 32; ++j) {
+        uint32_t* c = &cta_cnt[tid * 32 + ((j + lane) & 31)];
+        const uint32_t v = *c;
+        *c = run;
+        run += v;
+      }
     } else {
       uint32_t run = start;
 #pragma unroll
@@ -274,7 +341,7 @@ __device__ __forceinline__ void pass_tile(PassSmemT<WIDE>& S, const uint32_t* __
     // no earlier order to keep: a key takes the next free position of its digit
 #pragma unroll
     for (int i = 0; i < kItems; ++i)
-      if (FULL || (w_off + i * 32) < n_valid) S.keys[take_slot(key[i], sel, tbl)] = key[i];
+      if (FULL || (w_off + i * 32) < n_valid) S.keys[take_slot<128>(key[i], sel, tbl)] = key[i];
   } else {
     const uint32_t lane_bit = 1u << lane;
     const uint32_t le_mask = 0xffffffffu >> (31 - lane);
@@ -298,8 +365,22 @@ __device__ __forceinline__ void pass_tile(PassSmemT<WIDE>& S, const uint32_t* __
     }
   }
 
-  // ---- digit threads: decoupled look-back (two-level, see sweep_tile)
-  if (tid < kRadix) {
+  // ---- digit threads: where the tile's keys of each digit go in `out`
+  if (FIRST) {
+    // The first pass keeps no order, so the ORDER OF THE TILES inside a digit's output range
+    // does not matter either: each tile simply reserves its room with one atomicAdd per digit
+    // on the (scanned) histogram entry, instead of the look-back below, which accounted for
+    // 41% of this kernel's instructions and most of its barrier stall (ncu, v5b).
+    if (tid < kRadix) {
+      using Index = typename PassSmemT<WIDE>::Index;
+      unsigned long long first = 0;
+      if (count) first = atomicAdd(const_cast<unsigned long long*>(digit_base) + tid, (unsigned long long)count);
+      S.global_off[tid] = (Index)first - (Index)start;
+    }
+  } else if (tid < kRadix) {
+    // decoupled look-back, two levels: entries of my own group of kGroupTiles tiles first, then
+    // one entry per earlier group (the last tile of a group publishes the group's aggregate,
+    // later its inclusive sum)
     unsigned long long excl = 0;
     constexpr int kLook = B200_SORT_LOOK;
     auto walk = [&](const unsigned long long* arr, int64_t from, int64_t lo) -> bool {
@@ -330,12 +411,26 @@ __device__ __forceinline__ void pass_tile(PassSmemT<WIDE>& S, const uint32_t* __
       return inclusive;
     };
     const int64_t grp = tile / kGroupTiles, grp_begin = grp * kGroupTiles;
+    const bool group_first = (int64_t)tile == grp_begin;
     const bool group_end = (tile % kGroupTiles) == kGroupTiles - 1;
+    // third array: what precedes a whole group, found ONCE per group by its first tile (the
+    // oldest, so the first to get here); the other fifteen wait for that word instead of
+    // walking the group level themselves - that walk was most of the ~60 probes per tile
+    unsigned long long* group_excl = group_lb + (size_t)((gridDim.x + kGroupTiles - 1) / kGroupTiles) * kRadix;
     if (!walk(lookback, (int64_t)tile - 1, grp_begin)) {
       if (group_end)
         st_lookback(group_lb + (size_t)grp * kRadix + tid,
                     (kStAggregate << kStatusShift) | tag | (excl + count));
-      walk(group_lb, grp - 1, 0);
+      if (group_first) {
+        walk(group_lb, grp - 1, 0);  // excl was 0: now the sum of all earlier groups
+        st_lookback(group_excl + (size_t)grp * kRadix + tid, (kStInclusive << kStatusShift) | tag | excl);
+      } else {
+        unsigned long long e;
+        do {
+          e = ld_lookback(group_excl + (size_t)grp * kRadix + tid);
+        } while ((e >> kStatusShift) == 0 || ((e >> kPassShift) & 0xf) != (unsigned long long)pass);
+        excl += e & kValueMask;
+      }
     }
     if (group_end)
       st_lookback(group_lb + (size_t)grp * kRadix + tid,
@@ -372,9 +467,7 @@ __global__ void __launch_bounds__(kSortThreads, B200_SORT_PASS_BLOCKS)
   PassSmemT<WIDE>& S = *reinterpret_cast<PassSmemT<WIDE>*>(smem_raw);
   const int tid = threadIdx.x;
   if (tid == 0) S.tile_id = atomicAdd(ticket, 1u);
-  if (FIRST) {  // only the CTA-wide digit counters are used
-    if (tid < kRadix) reinterpret_cast<uint32_t*>(&S.pair[0][0])[tid] = 0;
-  } else {  // each warp clears its own 2 KB of counter words
+  {  // each warp clears 2 KB of the counter words (its own pairs; a slice of the first pass's table)
     uint4* z = reinterpret_cast<uint4*>(S.pair[tid >> 5]);
 #pragma unroll
     for (int j = 0; j < kRadix * 8 / 16 / 32; ++j) z[(tid & 31) + 32 * j] = make_uint4(0, 0, 0, 0);
@@ -463,7 +556,7 @@ static SortScratch carve(void* scratch, size_t n) {
   s.lookback = (unsigned long long*)p;
   s.tiles = (n + kTile - 1) / kTile;
   p += s.tiles * kRadix * sizeof(unsigned long long);
-  p += ((s.tiles + kGroupTiles - 1) / kGroupTiles) * kRadix * sizeof(unsigned long long);  // group entries
+  p += 2 * ((s.tiles + kGroupTiles - 1) / kGroupTiles) * kRadix * sizeof(unsigned long long);  // group entries + group prefixes
   s.bytes = (size_t)(p - (uint8_t*)scratch);
   return s;
 }
@@ -512,7 +605,18 @@ static int sort32(const uint32_t* input, uint32_t* keys, uint32_t* tmp, size_t n
     size_t min_blocks = (n >> 22) + 1;
     size_t blocks = want < (size_t)sms * 8 ? want : (size_t)sms * 8;
     if (blocks < min_blocks) blocks = min_blocks;
-    sort_hist_kernel<KT><<<(unsigned)blocks, kHistThreads, 0, st>>>(input, n, n_dev, sc.hist);
+    if (n >= (size_t(1) << 21)) {  // enough keys to amortise 128 KB of counters per CTA
+      static PerDeviceOnce hist_once;
+      if (int rc = hist_once.run("sort", [&]() -> int {
+            B200_CUDA_OK(cudaFuncSetAttribute(sort_hist_lanes_kernel<KT>,
+                                              cudaFuncAttributeMaxDynamicSharedMemorySize, kHist2Smem));
+            return 0;
+          }))
+        return rc;
+      sort_hist_lanes_kernel<KT><<<(unsigned)sms, kHist2Threads, kHist2Smem, st>>>(input, n, n_dev, sc.hist);
+    } else {
+      sort_hist_kernel<KT><<<(unsigned)blocks, kHistThreads, 0, st>>>(input, n, n_dev, sc.hist);
+    }
     B200_LAUNCH_OK();
   }
   sort_scan_kernel<<<1, kRadix, 0, st>>>(sc.hist, 4);
@@ -631,7 +735,7 @@ constexpr size_t kNoAllocMaxKeys = B200_SORT_NOALLOC_MAX_KEYS;
 constexpr size_t kNoAllocBookBytes =
     (4 * kRadix * sizeof(unsigned long long) + 64 +
      ((kNoAllocMaxKeys + kTile - 1) / kTile) * kRadix * sizeof(unsigned long long) +
-     (((kNoAllocMaxKeys + kTile - 1) / kTile + kGroupTiles - 1) / kGroupTiles) * kRadix *
+     2 * (((kNoAllocMaxKeys + kTile - 1) / kTile + kGroupTiles - 1) / kGroupTiles) * kRadix *
          sizeof(unsigned long long) +
      255) / 256 * 256;
 constexpr size_t kNoAllocBytes = kNoAllocBookBytes + kNoAllocMaxKeys * sizeof(uint32_t);
@@ -706,6 +810,7 @@ extern "C" int b200_preload_lab5(int key_type) {
   auto passes = [](auto kt) -> int {
     constexpr int KT = decltype(kt)::value;
     if (int rc = preload_kernel(sort_hist_kernel<KT>)) return rc;
+    if (int rc = preload_kernel(sort_hist_lanes_kernel<KT>)) return rc;
     if (int rc = preload_kernel(sort_pass_kernel<KT, true, false, false>)) return rc;
     if (int rc = preload_kernel(sort_pass_kernel<KT, false, false, false>)) return rc;
     return preload_kernel(sort_pass_kernel<KT, false, true, false>);

@@ -139,7 +139,7 @@ int b200_sort_devn(void* keys, void* tmp, size_t n, const unsigned long long* n_
  *  - all calls on a GPU share the array: calls that may overlap there (other
  *    streams or threads) race — keep them on one stream or order them. */
 #define B200_SORT_NOALLOC_MAX_KEYS (1u << 20)
-#define B200_SORT_NOALLOC_SCRATCH_BYTES 4481280u
+#define B200_SORT_NOALLOC_SCRATCH_BYTES 4497664u
 int b200_sort_noalloc(const void* input, void* output, size_t n, int key_type,
                       b200_stream_t s);
 
