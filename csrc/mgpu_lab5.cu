@@ -19,6 +19,8 @@
 //   3. local radix sort of the bucket, its length read on the device (lab5_sort.cu).
 // The phase masks exist so that virtual ranks can be exercised on one GPU without
 // kernels waiting on each other.  (No counterpart in the reference.)
+#include <cstdlib>
+
 #include "common.cuh"
 #include "symm.cuh"
 
@@ -248,6 +250,9 @@ __global__ void __launch_bounds__(kCountThreads)
 // 512 threads x 2 CTAs per SM.  (256 x 4 was a few percent faster with all eight "ranks"
 // on one GPU, but slower over real NVLink — 3.25 vs 2.9 ms at 8 GPUs: twice the remote
 // reservations and half the run length per destination.)
+#ifndef B200_PART_BLOCKS
+#define B200_PART_BLOCKS 2
+#endif
 constexpr int kPartThreads = 512;
 constexpr int kPartWarps = kPartThreads / 32;
 constexpr int kPartItems = 16;
@@ -273,8 +278,8 @@ struct PartTargets {
 //    destination, and a key's slot is that plus its rank among the thread's own keys
 //    (private shared-memory counters instead of registers were measured slower: LSU-bound);
 //  * the destination byte is staged beside the key, so the output loop does not search.
-template <int KT>
-__global__ void __launch_bounds__(kPartThreads, 1024 / kPartThreads)
+template <int KT, int BLOCKS>
+__global__ void __launch_bounds__(kPartThreads, BLOCKS)
     sort_partition_scatter_kernel(const uint32_t* __restrict__ keys, unsigned long long n_local,
                                   const unsigned long long* __restrict__ splitters, int idx_bits,
                                   PartTargets tg, unsigned long long capacity, SymmPeers peers,
@@ -564,15 +569,22 @@ extern "C" int b200_sort_mgpu_scatter(const void* keys, size_t n_local, int key_
   }
   const int idx_bits = idx_bits_for(world);
   B200_REQUIRE(n_local > 0, "sort_mgpu: empty shards are not supported");
+  // CTAs per SM the kernel is compiled for: 2 (64 registers) or 3 (40 registers, a few spills,
+  // more tiles in flight to hide the remote reservations); B200LABS_PART_BLOCKS overrides
+  static const int part_blocks = [] {
+    const char* e = getenv("B200LABS_PART_BLOCKS");
+    const int v = e ? atoi(e) : B200_PART_BLOCKS;
+    return v == 3 ? 3 : 2;
+  }();
   unsigned grid = 1u;
   if (phase_mask & 1) {
     const size_t tiles = (n_local + kPartTile - 1) / kPartTile;
-    const size_t resident = (size_t)device_info().sm_count * (1024 / kPartThreads);
+    const size_t resident = (size_t)device_info().sm_count * part_blocks;
     grid = (unsigned)(tiles < resident ? tiles : resident);
   }
   cudaStream_t st = as_stream(s);
 #define LAUNCH_PART(KT)                                                                         \
-  sort_partition_scatter_kernel<KT><<<grid, kPartThreads, 0, st>>>(                             \
+  (part_blocks == 3 ? sort_partition_scatter_kernel<KT, 3> : sort_partition_scatter_kernel<KT, 2>)<<<grid, kPartThreads, 0, st>>>( \
       (const uint32_t*)keys, n_local, (const unsigned long long*)splitters, idx_bits, tg,       \
       capacity, peers, rank, world, epoch, phase_mask, kDefaultTimeoutNs)
   switch (key_type) {

@@ -33,6 +33,44 @@ __global__ void symm_barrier_kernel(SymmPeers peers, int rank, int world, uint64
 
 using namespace b200;
 
+// ---- self-test: what a kernel gets out of NVLink, by access width ------------------------
+// mode 0: 4-byte stores (a warp writes 128 contiguous bytes), 1: 16-byte stores, 2: 4-byte
+// loads, 3: 16-byte loads, 4: 16 KB cp.async.bulk (TMA) stores out of shared memory.
+// `far` is a peer mapping, `near` local memory; n in 32-bit words, a multiple of 4096.
+namespace b200 {
+__global__ void __launch_bounds__(256) peer_copy_kernel(uint32_t* far, uint32_t* near, size_t n, int mode) {
+  __shared__ __align__(128) uint32_t stage[4096];
+  __shared__ __align__(8) uint64_t bar;
+  const size_t tid = blockIdx.x * (size_t)blockDim.x + threadIdx.x, nth = (size_t)gridDim.x * blockDim.x;
+  if (mode == 0) {
+    for (size_t i = tid; i < n; i += nth) far[i] = near[i];
+  } else if (mode == 1) {
+    for (size_t i = tid; i < n / 4; i += nth) reinterpret_cast<uint4*>(far)[i] = reinterpret_cast<const uint4*>(near)[i];
+  } else if (mode == 2) {
+    for (size_t i = tid; i < n; i += nth) near[i] = far[i];
+  } else if (mode == 3) {
+    for (size_t i = tid; i < n / 4; i += nth) reinterpret_cast<uint4*>(near)[i] = reinterpret_cast<const uint4*>(far)[i];
+  } else {
+    (void)bar;
+    for (size_t c = blockIdx.x; c < n / 4096; c += gridDim.x) {
+      for (int j = threadIdx.x; j < 1024; j += 256)
+        reinterpret_cast<uint4*>(stage)[j] = reinterpret_cast<const uint4*>(near + c * 4096)[j];
+      fence_proxy_async_smem();
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], 16384;" ::"l"(far + c * 4096),
+                     "r"(smem_u32(stage))
+                     : "memory");
+        tma_store_commit();
+        tma_store_wait_read<0>();  // the staging block may be refilled
+      }
+      __syncthreads();
+    }
+    if (threadIdx.x == 0) tma_store_wait<0>();
+  }
+}
+}  // namespace b200
+
 extern "C" {
 
 int b200_dev_malloc(void** p, size_t bytes) {
@@ -85,6 +123,13 @@ int b200_symm_barrier(const void* ws_ptrs, int rank, int world, uint64_t epoch,
                kMaxWorld);
   SymmPeers peers{(SymmWorkspace* const*)ws_ptrs};
   symm_barrier_kernel<<<1, 32, 0, as_stream(s)>>>(peers, rank, world, epoch, kDefaultTimeoutNs);
+  B200_LAUNCH_OK();
+  return 0;
+}
+
+int b200_selftest_peer_copy(void* far, void* near, size_t n_words, int mode, int blocks, b200_stream_t s) {
+  B200_REQUIRE(mode >= 0 && mode <= 4 && n_words % 4096 == 0 && blocks > 0, "peer_copy selftest: bad arguments");
+  peer_copy_kernel<<<blocks, 256, 0, as_stream(s)>>>((uint32_t*)far, (uint32_t*)near, n_words, mode);
   B200_LAUNCH_OK();
   return 0;
 }

@@ -188,6 +188,11 @@ int b200_mc_unbind(uint64_t mc, size_t bytes);
  * copies to out[i], mode 2 multimem.st stores value+i into every copy. */
 int b200_selftest_pingpong(void* my_flag, void* peer_flag, int initiator, int iters, uint64_t base,
                            int relaxed, void* out2_u64, b200_stream_t s);
+/* Kernel-driven copy between this GPU (`near_buf`) and a peer mapping (`far_buf`): mode 0 / 1 stores
+ * of 4 / 16 bytes per thread, 2 / 3 loads of 4 / 16 bytes, 4 TMA bulk stores of 16 KB out of
+ * shared memory.  n_words (32-bit) must be a multiple of 4096. */
+int b200_selftest_peer_copy(void* far_buf, void* near_buf, size_t n_words, int mode, int blocks,
+                            b200_stream_t s);
 int b200_selftest_multimem(void* mc_ptr, void* out, size_t n, int mode, uint64_t value,
                            b200_stream_t s);
 /* Stream-ordered barrier over peer memory: signal every rank, wait for every rank.

@@ -38,9 +38,11 @@ def main():
         t3 = timed(lambda: S.mgpu_scatter(m.keys, split, m.sym_bucket.peer_ptrs, None, m.capacity, m.ws, r, world,
                                           g.next_epoch(), 1 | 2 | (8 if m.reserve else 0)))
         t4 = timed(lambda: S.sort_devn(m.bucket, m.tmp, ws_local + m._off["sort_recv_count"], m.scratch))
+        m._settled = False
+        cnt, err = m.count(), g.ws_error()          # count() is collective: every rank calls it
         if r == 0:
             print(f"rep {rep}: splitters {t1:.3f} ms, count+reserve {t2:.3f} ms, scatter {t3:.3f} ms, "
-                  f"local sort {t4:.3f} ms, bucket {m.count()} keys, err {g.ws_error()}", flush=True)
+                  f"local sort {t4:.3f} ms, bucket {cnt} keys, err {err}", flush=True)
     g.barrier()
     torch.distributed.destroy_process_group()
 
