@@ -9,9 +9,10 @@ the exchange done by NCCL collectives through torch.distributed.
 from .symm import (PeerGroup, DistPeerGroup, LocalPeerGroup, SoloPeerGroup, SymmetricBuffer,
                    init_distributed)
 from . import vmm
-from .sharded import ShardedVectorSub, ShardedRoberts, ShardedClassifier, ShardedSort, shard_rows
+from .sharded import (ShardedVectorSub, ShardedRoberts, ShardedClassifier, ShardedSort, shard_rows,
+                      raise_on_error)
 
 __all__ = [
     "PeerGroup", "DistPeerGroup", "LocalPeerGroup", "SoloPeerGroup", "SymmetricBuffer", "init_distributed", "vmm",
-    "ShardedVectorSub", "ShardedRoberts", "ShardedClassifier", "ShardedSort", "shard_rows",
+    "ShardedVectorSub", "ShardedRoberts", "ShardedClassifier", "ShardedSort", "shard_rows", "raise_on_error",
 ]
