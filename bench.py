@@ -221,7 +221,7 @@ def run_own(args):
     fill_random_(model.band, seed=1234 + rank)
     group.barrier()
     launches0 = N.launch_count()
-    with ClockSampler(gpu_index=local_rank) as clocks:
+    with ClockSampler(gpu_index=local_rank, period_ms=1) as clocks:
         ms = timed_steps(group, model.step, args.steps, args.warmup)
     launches_timed = (N.launch_count() - launches0) * args.steps // (args.steps + args.warmup)
     clock_summary = clocks.summary()

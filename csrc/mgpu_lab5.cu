@@ -495,6 +495,205 @@ __global__ void __launch_bounds__(kPartThreads, BLOCKS)
   }
 }
 
+// ---- second form of the fused partition + exchange ----------------------------------------
+// Same job and same interface as the kernel above, built like the radix sort's first pass
+// (lab5_sort.cu): this step keeps no order, so a tile COUNTS its keys per destination on
+// (destination, lane) counters - one bank column per lane, conflict-free - turns the counters
+// into cursors and PLACES every key with one shared-memory atomic on its (destination, lane)
+// cursor.  No per-thread packed counters, no warp scans, three CTA barriers per tile instead of
+// five, keys loaded as 16-byte vectors (a partition need not see them in memory order), and two
+// counter sets used in turn so that clearing one never waits for the other.
+struct Part2Smem {
+  uint32_t keys[kPartTile];            // keys in destination order
+  uint8_t dst[kPartTile];              // their destinations
+  uint8_t dest_lut[1 << kDestLutBits];
+  uint32_t cnt[2][kMaxWorld][32];      // [set][destination][lane]: counts, then cursors
+  uint32_t* bias[kMaxWorld + 1];       // bucket + reserved base - tile start; null = dropped
+  uint32_t hi[kMaxWorld], lo[kMaxWorld];
+  uint32_t* bucket[kMaxWorld];
+  unsigned long long* cursor[kMaxWorld];
+  bool is_last;
+};
+
+template <int KT, int BLOCKS>
+__global__ void __launch_bounds__(kPartThreads, BLOCKS)
+    sort_partition_scatter2_kernel(const uint32_t* __restrict__ keys, unsigned long long n_local,
+                                   const unsigned long long* __restrict__ splitters, int idx_bits,
+                                   PartTargets tg, unsigned long long capacity, SymmPeers peers,
+                                   int rank, int world, uint64_t epoch, int phase_mask,
+                                   unsigned long long timeout_ns) {
+  extern __shared__ __align__(16) uint8_t part_smem_raw[];
+  Part2Smem& S = *reinterpret_cast<Part2Smem*>(part_smem_raw);
+  SymmWorkspace* me = peers.ws[rank];
+  const int tid = threadIdx.x, lane = tid & 31;
+
+  if (phase_mask & 1) {
+    if (tid < kMaxWorld) {
+      const unsigned long long sp = tid < world ? splitters[tid] : ~0ull;
+      S.hi[tid] = (uint32_t)(sp >> 32);
+      S.lo[tid] = (uint32_t)sp;
+      S.bucket[tid] = tg.bucket[tid];
+      S.cursor[tid] = tg.cursor[tid];
+    }
+    if (tid == 0) S.bias[kMaxWorld] = nullptr;
+    for (int i = tid; i < 2 * kMaxWorld * 32; i += kPartThreads) (&S.cnt[0][0][0])[i] = 0;
+    __syncthreads();
+    // ---- destination table over [first splitter key, last splitter key] (as above)
+    const uint32_t lut_base = world > 1 ? S.hi[1] : 0xffffffffu;
+    const uint32_t lut_span = world > 1 ? S.hi[world - 1] - lut_base : 0u;
+    const int lut_shift = lut_span < (1u << kDestLutBits) ? 0 : 32 - kDestLutBits - __clz(lut_span);
+    for (int bkt = tid; bkt < (1 << kDestLutBits); bkt += kPartThreads) {
+      const unsigned long long lo = (unsigned long long)lut_base + ((unsigned long long)bkt << lut_shift);
+      const unsigned long long hi = lo + ((1ull << lut_shift) - 1);
+      uint32_t below = 0, upto = 0;
+#pragma unroll
+      for (int k = 1; k < kMaxWorld; ++k)
+        if (k < world) {
+          below += (unsigned long long)S.hi[k] < lo ? 1u : 0u;
+          upto += (unsigned long long)S.hi[k] <= hi ? 1u : 0u;
+        }
+      S.dest_lut[bkt] = (uint8_t)(below | (upto != below ? kDestAmbiguous : 0u));
+    }
+    __syncthreads();
+    const uint32_t src_bits = idx_bits >= 32 ? 0u : ((uint32_t)rank << idx_bits);
+    const unsigned long long n_tiles = (n_local + kPartTile - 1) / kPartTile;
+    const bool aligned = (((uintptr_t)keys) & 15u) == 0;
+    int set = 0;
+    // persistent: a CTA walks tiles blockIdx.x, +gridDim.x, ... and fences its remote stores ONCE
+    // at the end (a system-scope fence per tile costs an NVLink round trip per tile)
+    for (unsigned long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, set ^= 1) {
+      const unsigned long long tile_base = tile * kPartTile;
+      const uint32_t n_valid = (uint32_t)min((unsigned long long)kPartTile, n_local - tile_base);
+      // ---- load: thread t owns elements (j * 512 + t) * 4 + k of the tile
+      uint32_t key[kPartItems];
+#pragma unroll
+      for (int j = 0; j < kPartItems / 4; ++j) {
+        const uint32_t o = (j * kPartThreads + tid) * 4;
+        if (aligned && o + 3 < n_valid) {
+          const uint4 v = ld_stream_u4(keys + tile_base + o);
+          key[4 * j] = v.x, key[4 * j + 1] = v.y, key[4 * j + 2] = v.z, key[4 * j + 3] = v.w;
+        } else {
+#pragma unroll
+          for (int k = 0; k < 4; ++k) key[4 * j + k] = o + k < n_valid ? ld_stream_u32(keys + tile_base + o + k) : 0u;
+        }
+      }
+      // ---- destinations (table; exact comparison only next to a splitter), 4 bits per key
+      unsigned long long meta = 0;
+      const uint32_t cnt_base = smem_u32(&S.cnt[set][0][0]) + 4u * lane;
+#pragma unroll
+      for (int i = 0; i < kPartItems; ++i) {
+        const uint32_t o = ((i >> 2) * kPartThreads + tid) * 4 + (i & 3);
+        const uint32_t x = to_ordered_mg<KT>(key[i]);
+        const uint32_t t = (x - lut_base) >> lut_shift;
+        uint32_t e = S.dest_lut[t < (1u << kDestLutBits) ? t : 0u];
+        e = t < (1u << kDestLutBits) ? e : (uint32_t)(world - 1);  // above every splitter
+        e = x < lut_base ? 0u : e;                                  // below every splitter
+        if (e & kDestAmbiguous) {
+          const uint32_t low = src_bits | (uint32_t)(tile_base + o);
+          e = 0;
+#pragma unroll
+          for (int k = 1; k < kMaxWorld; ++k)
+            if (k < world) e += (S.hi[k] < x || (S.hi[k] == x && S.lo[k] <= low)) ? 1u : 0u;
+        }
+        e = o < n_valid ? e : kNoDest;
+        meta |= (unsigned long long)e << (4 * i);
+        if (e < kNoDest) asm volatile("red.shared.add.u32 [%0], 1;" ::"r"(cnt_base + e * 128u) : "memory");
+      }
+      __syncthreads();
+      // ---- per destination: total, reservation in the destination's bucket, cursors
+      unsigned long long b = 0;
+      uint32_t total = 0, start = 0;
+      if (tid < kMaxWorld) {
+        uint32_t* row = S.cnt[set][tid];
+        const int rot = 4 * tid;  // the eight threads walk their rows through different banks
+#pragma unroll 8
+        for (int j = 0; j < 32; ++j) total += row[(j + rot) & 31];
+        // The (mostly remote) atomic's result is not touched until the keys are placed, so its
+        // NVLink round trip overlaps the placement.
+        if (tid < world && total) {
+          if (phase_mask & 8)
+            b = atomicAdd(&me->sort_local_cursor[tid], (unsigned long long)total);
+          else
+            b = atomicAdd_system(S.cursor[tid], (unsigned long long)total);
+        }
+        uint32_t inc = total;
+#pragma unroll
+        for (int o = 1; o < kMaxWorld; o <<= 1) {
+          const uint32_t t = __shfl_up_sync(0xffu, inc, o);
+          if (tid >= o) inc += t;
+        }
+        start = inc - total;
+        uint32_t run = start;
+#pragma unroll 8
+        for (int j = 0; j < 32; ++j) {
+          uint32_t* c = &row[(j + rot) & 31];
+          const uint32_t v = *c;
+          *c = run;
+          run += v;
+        }
+      } else if (tid >= kPartThreads - kMaxWorld * 32) {
+        // the other counter set (last used by the previous tile's placement) is cleared here
+        (&S.cnt[set ^ 1][0][0])[tid - (kPartThreads - kMaxWorld * 32)] = 0;
+      }
+      __syncthreads();
+      // ---- place: one shared-memory atomic per key on its (destination, lane) cursor
+#pragma unroll
+      for (int i = 0; i < kPartItems; ++i) {
+        const uint32_t e = (uint32_t)(meta >> (4 * i)) & 0xfu;
+        if (e < kNoDest) {
+          uint32_t pos;
+          asm volatile("atom.shared.add.u32 %0, [%1], 1;" : "=r"(pos) : "r"(cnt_base + e * 128u) : "memory");
+          S.keys[pos] = key[i];
+          S.dst[pos] = (uint8_t)e;
+        }
+      }
+      if (tid < kMaxWorld) {
+        if (tid < world && b + total > capacity) {
+          // overflow (or, with bit 8, a reservation that failed earlier): this tile's keys for that
+          // destination are dropped and the error word says so (the host grows the buckets and re-runs)
+          if (!(phase_mask & 8)) atomicOr(&me->error, (unsigned long long)kErrSortOverflow);
+          b = ~0ull;
+        }
+        S.bias[tid] = (tid < world && b != ~0ull) ? S.bucket[tid] + b - start : nullptr;
+      }
+      __syncthreads();
+      // ---- runs of equal destination leave as contiguous (mostly remote) stores
+#pragma unroll
+      for (int i = 0; i < kPartItems; ++i) {
+        const uint32_t p = tid + i * kPartThreads;
+        if (p < n_valid) {
+          uint32_t* dst = S.bias[S.dst[p]];
+          if (dst) dst[p] = S.keys[p];
+        }
+      }
+      // no barrier here: the next tile counts on the OTHER counter set, and its placement into
+      // S.keys / S.dst comes after two more barriers, i.e. after every thread has left this loop
+    }
+    // ---- ticket: last CTA tells every peer that this rank has finished writing
+    __threadfence_system();
+    __syncthreads();
+    if (tid == 0) S.is_last = atomicAdd(&me->sort_blocks_done, 1u) == gridDim.x - 1;
+    __syncthreads();
+    if (!S.is_last) return;
+    if (!(phase_mask & 4)) {  // bit 2 set: local-only partition (NCCL baseline), no signalling
+      if (tid == 0) me->sort_blocks_done = 0;
+      __threadfence_system();
+      if (tid < world) signal_peer(peers, tid, rank, epoch, kFlagSortDone);
+    } else if (tid == 0) {
+      me->sort_blocks_done = 0;
+    }
+  }
+  if ((phase_mask & 2) && !(phase_mask & 4)) {
+    if (tid < world) wait_peer(peers, rank, tid, epoch, timeout_ns, kFlagSortDone);
+    __syncthreads();
+    if (tid == 0) {
+      unsigned long long c;
+      asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(c) : "l"(&me->sort_cursor) : "memory");
+      me->sort_recv_count = c < capacity ? c : capacity;
+    }
+  }
+}
+
 }  // namespace b200
 
 using namespace b200;
@@ -583,10 +782,21 @@ extern "C" int b200_sort_mgpu_scatter(const void* keys, size_t n_local, int key_
     grid = (unsigned)(tiles < resident ? tiles : resident);
   }
   cudaStream_t st = as_stream(s);
+  // B200LABS_PART_IMPL=1 selects the first form of the kernel (packed register counters + warp scans)
+  static const int part_impl = [] {
+    const char* e = getenv("B200LABS_PART_IMPL");
+    return e ? atoi(e) : 2;
+  }();
+  static_assert(sizeof(Part2Smem) <= 48 * 1024, "Part2Smem must fit the default dynamic shared memory limit");
 #define LAUNCH_PART(KT)                                                                         \
-  (part_blocks == 3 ? sort_partition_scatter_kernel<KT, 3> : sort_partition_scatter_kernel<KT, 2>)<<<grid, kPartThreads, 0, st>>>( \
-      (const uint32_t*)keys, n_local, (const unsigned long long*)splitters, idx_bits, tg,       \
-      capacity, peers, rank, world, epoch, phase_mask, kDefaultTimeoutNs)
+  if (part_impl == 1)                                                                           \
+    (part_blocks == 3 ? sort_partition_scatter_kernel<KT, 3> : sort_partition_scatter_kernel<KT, 2>)<<<grid, kPartThreads, 0, st>>>( \
+        (const uint32_t*)keys, n_local, (const unsigned long long*)splitters, idx_bits, tg,     \
+        capacity, peers, rank, world, epoch, phase_mask, kDefaultTimeoutNs);                    \
+  else                                                                                          \
+    (part_blocks == 3 ? sort_partition_scatter2_kernel<KT, 3> : sort_partition_scatter2_kernel<KT, 2>)<<<grid, kPartThreads, sizeof(Part2Smem), st>>>( \
+        (const uint32_t*)keys, n_local, (const unsigned long long*)splitters, idx_bits, tg,     \
+        capacity, peers, rank, world, epoch, phase_mask, kDefaultTimeoutNs)
   switch (key_type) {
     case B200_KEY_I32: LAUNCH_PART(B200_KEY_I32); break;
     case B200_KEY_U32: LAUNCH_PART(B200_KEY_U32); break;
