@@ -1,10 +1,6 @@
 """CUDA-graph replay of the launch-bound sequences (utils/graphs.py): a captured sort and a
 captured lab3 step must give, on every replay and for new buffer contents, exactly what the
-eager path gives.
-
-NOT collected automatically (file name): utils/graphs.py has not passed on hardware yet, see
-its docstring.  Run with `python -m pytest tests/manual_gpu_graphs.py -q` on a GPU box and
-rename to test_gpu_graphs.py when green."""
+eager path gives."""
 import numpy as np
 import pytest
 import torch
