@@ -397,7 +397,7 @@ def verify_lab3(group, m3, classes, size):
 
     world, rank = group.world, group.rank
     m3.step()
-    torch.cuda.synchronize()
+    m3.check()                                            # raises on an in-kernel peer time-out
     band = m3.band.cpu().numpy()                          # RGB untouched by classify, alpha = class
     pts, off = CL.pack_points(classes, w=size, h=size)
     mom = np.zeros((len(classes), CL.N_MOMENTS), dtype=np.int64)
@@ -477,7 +477,6 @@ def run_reference(args):
             print(json.dumps({"impl": "reference", "unavailable":
                               "baseline/_ref/bin/lab2_to_plot missing (run baseline/install_reference.sh)"}))
         return
-    import numpy as np
 
     dist = None
     if world > 1:

@@ -224,13 +224,13 @@ __device__ __forceinline__ void sts_pair(unsigned long long* p, uint32_t lo, uin
 }
 // counter[digit(key)] += 1 with the digit and the address formed inside one statement, so the
 // compiler cannot hoist sixteen addresses above the loop (it spilled the KEYS to do that)
-template <int STRIDE>  // bytes per table entry; the counter is the entry's LAST 32-bit word
+template <int STRIDE, int OFFSET>  // bytes per table entry, byte offset of the counter inside it
 __device__ __forceinline__ void count_digit(uint32_t key, uint32_t sel, uint32_t table_smem) {
   asm volatile(
       "{\n\t.reg .b32 d, a;\n\t"
       "prmt.b32 d, %0, 0, %1;\n\t"
       "mad.lo.u32 a, d, %3, %2;\n\t"
-      "red.shared.add.u32 [a+%4], 1;\n\t}" ::"r"(key), "r"(sel), "r"(table_smem), "n"(STRIDE), "n"(STRIDE - 4)
+      "red.shared.add.u32 [a+%4], 1;\n\t}" ::"r"(key), "r"(sel), "r"(table_smem), "n"(STRIDE), "n"(OFFSET)
       : "memory");
 }
 // position = cursor[digit(key)]++ on a table of STRIDE-byte entries
@@ -280,13 +280,12 @@ __device__ __forceinline__ void pass_tile(PassSmemT<WIDE>& S, const uint32_t* __
     if (FIRST) k = to_ordered<KT>(k);
     key[i] = k;
   }
-  // count_digit adds STRIDE - 4 to the entry address: bias the lane-column table accordingly
   const uint32_t tbl = FIRST ? smem_u32(cta_cnt) + 4u * lane : smem_u32(pr);
 #pragma unroll
   for (int i = 0; i < kItems; ++i)
     if (FULL || (w_off + i * 32) < n_valid) {
-      if (FIRST) count_digit<128>(key[i], sel, tbl - 124u);
-      else count_digit<8>(key[i], sel, tbl);
+      if (FIRST) count_digit<128, 0>(key[i], sel, tbl);  // (digit, lane) counter: 32 words per digit
+      else count_digit<8, 4>(key[i], sel, tbl);          // high half of the warp's {mask, position} pair
     }
   __syncthreads();
 

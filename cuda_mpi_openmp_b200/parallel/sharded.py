@@ -340,6 +340,13 @@ class ShardedClassifier:
             return apply_lut2(self.band, self._lut_local)
         return CL.lab3_classify(self.band, self.params, variant=self.variant, scratch=self.scratch)
 
+    def check(self) -> None:
+        """Call at a point where the stream may be synchronised: raises if an in-kernel wait for a
+        peer timed out during the steps so far (parameters and classes would then be garbage)."""
+        torch.cuda.synchronize(self.group.device)
+        if self.group.world > 1:
+            raise_on_error(self.group, "ShardedClassifier")
+
     def free(self) -> None:
         if self.sym_lut is not None:
             self.sym_lut.free()

@@ -1,9 +1,8 @@
 #!/usr/bin/env python
 """lab5 radix sort: correctness + device time for one library configuration.
 
-The pass-kernel variants are picked by environment variables that the library reads
-once per process (B200LABS_SORT_IMPL, B200LABS_SORT_BLOCKS), so each configuration is
-its own process:  B200LABS_SORT_IMPL=4 python tools/sort_bench.py --n 26 --dist uniform
+Library variants (another build via B200LABS_LIB=<path to .so>) are read once per process,
+so each configuration is its own process:  python tools/sort_bench.py --n 26 --dist uniform
 
 Sorting is timed out of place (b200_sort_ex reads `src`, writes `keys`), so no copy is
 inside the timed region.  Every distribution is checked against torch.sort once."""
@@ -58,7 +57,7 @@ def main():
     args = ap.parse_args()
     dev = torch.device("cuda:0")
     dtype = {"int32": torch.int32, "float32": torch.float32}[args.dtype]
-    tag = {k: os.environ.get(k, "") for k in ("B200LABS_SORT_IMPL", "B200LABS_SORT_NB", "B200LABS_SORT_FIRST_BLOCKS")}
+    tag = {"lib": os.environ.get("B200LABS_LIB", "default")}
     rows = []
     for lg in [int(v) for v in args.n.split(",")]:
         n = 1 << lg
