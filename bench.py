@@ -120,6 +120,14 @@ def own_binary_e2e(args, group, rank, world, local_rank, w, h):
             if label == "whole_band" and n_chunks == 1:
                 res[label] = "same as chunked (the band is one chunk)"
                 continue
+            # input + output file of every rank must fit the RAM disk: decided together, so that no
+            # rank leaves the others waiting in a barrier
+            import shutil
+            need = 2 * (8 + 4 * w * rows) * world + (1 << 30)
+            short = group.all_reduce_max(1.0 if shutil.disk_usage(shm).free < need else 0.0) > 0
+            if short:
+                res[label] = f"skipped: {shm} has less than {need >> 30} GiB free"
+                continue
             write_synthetic_image(in_path, w, rows, seed=1234 + rank)
             stdin = f"-1\n-1\n-1\n-1\n{in_path}\n{out_path}\n"
             group.barrier()
