@@ -248,6 +248,10 @@ __device__ __forceinline__ uint32_t take_slot(uint32_t key, uint32_t sel, uint32
   return r;
 }
 
+__device__ __forceinline__ void pr_hi_add(unsigned long long* pr, uint32_t d, uint32_t v) {
+  atomicAdd(reinterpret_cast<uint32_t*>(&pr[d]) + 1, v);
+}
+
 template <int KT>
 __device__ __forceinline__ uint32_t from_ordered(uint32_t o) {
   if (KT == B200_KEY_I32) return o ^ 0x80000000u;
@@ -281,11 +285,24 @@ __device__ __forceinline__ void pass_tile(PassSmemT<WIDE>& S, const uint32_t* __
     key[i] = k;
   }
   const uint32_t tbl = FIRST ? smem_u32(cta_cnt) + 4u * lane : smem_u32(pr);
+  // Rows whose 32 keys share ONE digit (sorted or low-entropy input: the upper digits of a tile are
+  // constant) would send 32 atomics to one shared word, which serialise; such a row is counted
+  // and ranked by a single lane instead.  Bit i of `uniform_rows` marks row i.
+  uint32_t uniform_rows = 0;
 #pragma unroll
   for (int i = 0; i < kItems; ++i)
     if (FULL || (w_off + i * 32) < n_valid) {
-      if (FIRST) count_digit<128, 0>(key[i], sel, tbl);  // (digit, lane) counter: 32 words per digit
-      else count_digit<8, 4>(key[i], sel, tbl);          // high half of the warp's {mask, position} pair
+      if (FIRST) {
+        count_digit<128, 0>(key[i], sel, tbl);  // (digit, lane) counter: 32 words per digit, no conflicts
+      } else {
+        const uint32_t d = __byte_perm(key[i], 0, sel);
+        if (FULL && __all_sync(0xffffffffu, d == __shfl_sync(0xffffffffu, d, 0))) {
+          uniform_rows |= 1u << i;
+          if (lane == 0) pr_hi_add(pr, d, 32u);
+        } else {
+          count_digit<8, 4>(key[i], sel, tbl);  // high half of the warp's {mask, position} pair
+        }
+      }
     }
   __syncthreads();
 
@@ -348,6 +365,14 @@ __device__ __forceinline__ void pass_tile(PassSmemT<WIDE>& S, const uint32_t* __
     for (int i = 0; i < kItems; ++i) {
       const uint32_t d = __byte_perm(key[i], 0, sel);
       const bool valid = FULL || (w_off + i * 32) < n_valid;
+      if (FULL && (uniform_rows >> i & 1u)) {  // warp-uniform: the whole row is one group, in lane order
+        const uint2 v = lds_pair(&pr[d]);      // same word for every lane: a broadcast
+        __syncwarp();
+        if (lane == 31) sts_pair(&pr[d], 0u, v.y + 32u);
+        S.keys[v.y + lane] = key[i];
+        __syncwarp();
+        continue;
+      }
       if (valid) atomicOr(reinterpret_cast<uint32_t*>(&pr[d]), lane_bit);
       __syncwarp();
       uint2 v = make_uint2(0u, 0u);  // {lanes of this row with my digit, next free position}
