@@ -285,25 +285,39 @@ __device__ __forceinline__ void pass_tile(PassSmemT<WIDE>& S, const uint32_t* __
     key[i] = k;
   }
   const uint32_t tbl = FIRST ? smem_u32(cta_cnt) + 4u * lane : smem_u32(pr);
-  // Rows whose 32 keys share ONE digit (sorted or low-entropy input: the upper digits of a tile are
-  // constant) would send 32 atomics to one shared word, which serialise; such a row is counted
-  // and ranked by a single lane instead.  Bit i of `uniform_rows` marks row i.
-  uint32_t uniform_rows = 0;
+  // A warp whose 512 keys share ONE digit, or one digit per half (low-entropy or sorted input:
+  // the upper digits of a tile are constant over long runs) would send every atomic of every
+  // row to one shared word, where they serialise (2^26 equal keys: 1.59 ms against 1.21 for
+  // random ones).  Such a warp counts and ranks without atomics.  Random digits pay two votes
+  // per tile for the test.
+  bool warp_uniform = false;
+  uint32_t d_lo = 0, d_hi = 0;  // digit of rows [0, kItems/2) and of rows [kItems/2, kItems)
+  if (!FIRST && FULL) {
+    d_lo = __byte_perm(key[0], 0, sel);
+    d_hi = __byte_perm(key[kItems - 1], 0, sel);
+    // both shuffles outside the condition: `&&` would skip the second one on some lanes
+    const uint32_t lo0 = __shfl_sync(0xffffffffu, d_lo, 0), hi0 = __shfl_sync(0xffffffffu, d_hi, 0);
+    if (__all_sync(0xffffffffu, (d_lo ^ lo0 | d_hi ^ hi0) == 0)) {
+      uint32_t diff = 0;
 #pragma unroll
-  for (int i = 0; i < kItems; ++i)
-    if (FULL || (w_off + i * 32) < n_valid) {
-      if (FIRST) {
-        count_digit<128, 0>(key[i], sel, tbl);  // (digit, lane) counter: 32 words per digit, no conflicts
-      } else {
-        const uint32_t d = __byte_perm(key[i], 0, sel);
-        if (FULL && __all_sync(0xffffffffu, d == __shfl_sync(0xffffffffu, d, 0))) {
-          uniform_rows |= 1u << i;
-          if (lane == 0) pr_hi_add(pr, d, 32u);
-        } else {
-          count_digit<8, 4>(key[i], sel, tbl);  // high half of the warp's {mask, position} pair
-        }
-      }
+      for (int i = 1; i < kItems - 1; ++i)
+        diff |= __byte_perm(key[i], 0, sel) ^ (i < kItems / 2 ? d_lo : d_hi);
+      warp_uniform = __all_sync(0xffffffffu, diff == 0);
     }
+  }
+  if (warp_uniform) {
+    if (lane == 0) {
+      pr_hi_add(pr, d_lo, kItems * 16u);
+      pr_hi_add(pr, d_hi, kItems * 16u);
+    }
+  } else {
+#pragma unroll
+    for (int i = 0; i < kItems; ++i)
+      if (FULL || (w_off + i * 32) < n_valid) {
+        if (FIRST) count_digit<128, 0>(key[i], sel, tbl);  // (digit, lane) counter: 32 words per digit
+        else count_digit<8, 4>(key[i], sel, tbl);          // high half of the warp's {mask, position} pair
+      }
+  }
   __syncthreads();
 
   // ---- digit threads: counts -> tile positions, publish the aggregate, scan the digits
@@ -358,6 +372,13 @@ __device__ __forceinline__ void pass_tile(PassSmemT<WIDE>& S, const uint32_t* __
 #pragma unroll
     for (int i = 0; i < kItems; ++i)
       if (FULL || (w_off + i * 32) < n_valid) S.keys[take_slot<128>(key[i], sel, tbl)] = key[i];
+  } else if (warp_uniform) {
+    // each half is one group in memory order: positions base + row * 32 + lane
+    const uint32_t base_lo = lds_pair(&pr[d_lo]).y;
+    const uint32_t base_hi = d_hi == d_lo ? base_lo + kItems * 16u : lds_pair(&pr[d_hi]).y;
+#pragma unroll
+    for (int i = 0; i < kItems; ++i)
+      S.keys[(i < kItems / 2 ? base_lo + i * 32 : base_hi + (i - kItems / 2) * 32) + lane] = key[i];
   } else {
     const uint32_t lane_bit = 1u << lane;
     const uint32_t le_mask = 0xffffffffu >> (31 - lane);
@@ -365,14 +386,6 @@ __device__ __forceinline__ void pass_tile(PassSmemT<WIDE>& S, const uint32_t* __
     for (int i = 0; i < kItems; ++i) {
       const uint32_t d = __byte_perm(key[i], 0, sel);
       const bool valid = FULL || (w_off + i * 32) < n_valid;
-      if (FULL && (uniform_rows >> i & 1u)) {  // warp-uniform: the whole row is one group, in lane order
-        const uint2 v = lds_pair(&pr[d]);      // same word for every lane: a broadcast
-        __syncwarp();
-        if (lane == 31) sts_pair(&pr[d], 0u, v.y + 32u);
-        S.keys[v.y + lane] = key[i];
-        __syncwarp();
-        continue;
-      }
       if (valid) atomicOr(reinterpret_cast<uint32_t*>(&pr[d]), lane_bit);
       __syncwarp();
       uint2 v = make_uint2(0u, 0u);  // {lanes of this row with my digit, next free position}
