@@ -248,6 +248,13 @@ __device__ __forceinline__ uint32_t take_slot(uint32_t key, uint32_t sel, uint32
   return r;
 }
 
+// Where the key with tile position `pos` lives in PassSmem::keys: the low five bits are XORed with
+// the next five.  A tile of already ordered input has (about) equally many keys of each digit, so
+// the keys a warp places in one step go to positions a multiple of 32 apart - one bank without
+// the swizzle (sorted 2^26 keys: 1.44 ms against 1.21 for random ones).  Runs of 32 consecutive
+// positions stay conflict-free, so the output loop does not care.
+__device__ __forceinline__ uint32_t key_slot(uint32_t pos) { return pos ^ ((pos >> 5) & 31u); }
+
 __device__ __forceinline__ void pr_hi_add(unsigned long long* pr, uint32_t d, uint32_t v) {
   atomicAdd(reinterpret_cast<uint32_t*>(&pr[d]) + 1, v);
 }
@@ -371,14 +378,14 @@ __device__ __forceinline__ void pass_tile(PassSmemT<WIDE>& S, const uint32_t* __
     // no earlier order to keep: a key takes the next free position of its digit
 #pragma unroll
     for (int i = 0; i < kItems; ++i)
-      if (FULL || (w_off + i * 32) < n_valid) S.keys[take_slot<128>(key[i], sel, tbl)] = key[i];
+      if (FULL || (w_off + i * 32) < n_valid) S.keys[key_slot(take_slot<128>(key[i], sel, tbl))] = key[i];
   } else if (warp_uniform) {
     // each half is one group in memory order: positions base + row * 32 + lane
     const uint32_t base_lo = lds_pair(&pr[d_lo]).y;
     const uint32_t base_hi = d_hi == d_lo ? base_lo + kItems * 16u : lds_pair(&pr[d_hi]).y;
 #pragma unroll
     for (int i = 0; i < kItems; ++i)
-      S.keys[(i < kItems / 2 ? base_lo + i * 32 : base_hi + (i - kItems / 2) * 32) + lane] = key[i];
+      S.keys[key_slot((i < kItems / 2 ? base_lo + i * 32 : base_hi + (i - kItems / 2) * 32) + lane)] = key[i];
   } else {
     const uint32_t lane_bit = 1u << lane;
     const uint32_t le_mask = 0xffffffffu >> (31 - lane);
@@ -396,7 +403,7 @@ __device__ __forceinline__ void pass_tile(PassSmemT<WIDE>& S, const uint32_t* __
       const uint32_t next = pos + __popc(peers & le_mask);
       if (valid) {
         if ((peers >> lane) == 1u) sts_pair(&pr[d], 0u, next);
-        S.keys[next - 1] = key[i];
+        S.keys[key_slot(next - 1)] = key[i];
       }
       __syncwarp();
     }
@@ -486,7 +493,7 @@ __device__ __forceinline__ void pass_tile(PassSmemT<WIDE>& S, const uint32_t* __
   for (int i = 0; i < kItems; ++i) {
     const uint32_t p = tid + i * kSortThreads;
     if (FULL || p < n_valid) {
-      const uint32_t k = S.keys[p];
+      const uint32_t k = S.keys[key_slot(p)];
       const uint32_t d = __byte_perm(k, 0, sel);
       out[(typename PassSmemT<WIDE>::Index)(S.global_off[d] + p)] = LAST ? from_ordered<KT>(k) : k;
     }

@@ -276,6 +276,20 @@ def test_sort_matches_torch_and_oracle(cuda_device, dtype):
                 assert torch.equal(d, want_t)
 
 
+def test_sort_runs_of_equal_digits(cuda_device):
+    """Warps whose keys share a digit (per half or whole) take the atomic-free ranking path;
+    run lengths around 256 / 512 keys put the boundary inside, between and across warps."""
+    rng = np.random.default_rng(32)
+    n = 2_500_003
+    for run in [1, 100, 256, 300, 512, 8192, 100_000, n]:
+        hi = np.repeat(rng.integers(0, 1 << 24, n // run + 1, dtype=np.int64), run)[:n]
+        for low_bits in (0, 8):
+            k = ((hi << 8) | rng.integers(0, 1 << low_bits, n, dtype=np.int64)).astype(np.uint32).view(np.int32)
+            d = torch.from_numpy(k.copy()).to(cuda_device)
+            ops.sort_(d)
+            assert np.array_equal(d.cpu().numpy(), np.sort(k)), (run, low_bits)
+
+
 def test_sort_fixtures_and_host_pipeline(cuda_device, repo_root):
     for name, dt in [("int10", np.int32), ("float10", np.float32), ("uchar10", np.uint8)]:
         blob = (repo_root / "lab5/data" / name).read_bytes()
