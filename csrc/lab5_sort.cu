@@ -143,10 +143,21 @@ __global__ void __launch_bounds__(kHist2Threads, 1)
 
 // exclusive scan of each 256-bin histogram, in place: hist[p][d] -> first output
 // index of digit d in pass p
-__global__ void sort_scan_kernel(unsigned long long* __restrict__ hist, int passes) {
+// `one_bin[p]` (optional) is set when a single digit value holds every key of pass p: that pass
+// is then the identity permutation and the pass kernel only copies.
+__global__ void sort_scan_kernel(unsigned long long* __restrict__ hist, int passes,
+                                 uint32_t* __restrict__ one_bin) {
   __shared__ unsigned long long wsum[kRadix / 32];
   for (int p = 0; p < passes; ++p) {
     unsigned long long v = hist[p * kRadix + threadIdx.x];
+    if (one_bin && v != 0 && hist[p * kRadix + ((threadIdx.x + 1) & (kRadix - 1))] == 0) {
+      // my bin is occupied and the next one (cyclically) is not: all keys are here iff every
+      // other bin is empty too, i.e. iff exactly one thread gets this far and sees the total
+      unsigned long long total = 0;
+      for (int d = 0; d < kRadix; ++d) total += hist[p * kRadix + d];
+      if (v == total) one_bin[p] = 1u;
+    }
+    __syncthreads();  // the reads above come before the in-place writes below
     unsigned long long inc = v;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
@@ -166,6 +177,7 @@ __global__ void sort_scan_kernel(unsigned long long* __restrict__ hist, int pass
 constexpr unsigned long long kStatusShift = 62, kPassShift = 58;
 constexpr unsigned long long kValueMask = (1ull << kPassShift) - 1;
 constexpr unsigned long long kStAggregate = 1, kStInclusive = 2;
+constexpr int kOneBinFlags = 8;  // tickets[8 + pass]: pass is an identity permutation (sort_scan_kernel)
 constexpr int kGroupTiles = 16;  // look-back groups: [tiles][256] entries, then [groups][256] twice
 
 __device__ __forceinline__ unsigned long long ld_lookback(const unsigned long long* p) {
@@ -208,6 +220,7 @@ struct PassSmemT {
   Index global_off[kRadix];                     // index in `out` of (digit, tile position 0), modulo 2^bits
   uint32_t scan_tmp[kRadix / 32];
   uint32_t tile_id;
+  uint32_t one_bin;  // this pass is an identity permutation (sort_scan_kernel found one digit value)
 };
 #ifndef B200_SORT_PASS_BLOCKS
 #define B200_SORT_PASS_BLOCKS 3
@@ -510,7 +523,11 @@ __global__ void __launch_bounds__(kSortThreads, B200_SORT_PASS_BLOCKS)
   extern __shared__ __align__(16) uint8_t smem_raw[];
   PassSmemT<WIDE>& S = *reinterpret_cast<PassSmemT<WIDE>*>(smem_raw);
   const int tid = threadIdx.x;
-  if (tid == 0) S.tile_id = atomicAdd(ticket, 1u);
+  if (tid == 0) {  // the flag's load latency hides behind the ticket's
+    const uint32_t one_bin = ticket[kOneBinFlags];
+    S.tile_id = atomicAdd(ticket, 1u);
+    S.one_bin = one_bin;
+  }
   {  // each warp clears 2 KB of the counter words (its own pairs; a slice of the first pass's table)
     uint4* z = reinterpret_cast<uint4*>(S.pair[tid >> 5]);
 #pragma unroll
@@ -523,6 +540,19 @@ __global__ void __launch_bounds__(kSortThreads, B200_SORT_PASS_BLOCKS)
   if (n_dev) n = (size_t)*n_dev;
   if (tile_base >= n) return;  // grid was sized for the capacity, not the actual length
   const uint32_t n_valid = (uint32_t)min((size_t)kTile, n - tile_base);
+  if (S.one_bin) {
+    // every key has the same digit in this pass (small-range or low-entropy keys): keep the order
+#pragma unroll
+    for (int i = 0; i < kItems; ++i) {
+      const uint32_t p = tid + i * kSortThreads;
+      if (p < n_valid) {
+        uint32_t k = ld_stream_u32(in + tile_base + p);
+        if (FIRST) k = to_ordered<KT>(k);
+        out[tile_base + p] = LAST ? from_ordered<KT>(k) : k;
+      }
+    }
+    return;
+  }
   if (n_valid == kTile)
     pass_tile<KT, FIRST, LAST, true, WIDE>(S, in, out, tile_base, n_valid, tile, pass, digit_base, lookback,
                                          group_lb);
@@ -663,7 +693,7 @@ static int sort32(const uint32_t* input, uint32_t* keys, uint32_t* tmp, size_t n
     }
     B200_LAUNCH_OK();
   }
-  sort_scan_kernel<<<1, kRadix, 0, st>>>(sc.hist, 4);
+  sort_scan_kernel<<<1, kRadix, 0, st>>>(sc.hist, 4, sc.tickets + kOneBinFlags);
   B200_LAUNCH_OK();
   // n is the capacity (the upper bound on the length): below 2^32 every output index fits 32 bits
   if (n < (size_t(1) << 32)) return sort32_passes<KT, false>(input, keys, tmp, n, n_dev, sc, st);
@@ -727,7 +757,7 @@ extern "C" int b200_sort_ex(const void* input, void* keys, void* tmp, size_t n,
       sort_u8_hist_kernel<<<(unsigned)blocks, kHistThreads, 0, st>>>((const uint8_t*)keys, n,
                                                                      sc.hist);
       B200_LAUNCH_OK();
-      sort_scan_kernel<<<1, kRadix, 0, st>>>(sc.hist, 1);
+      sort_scan_kernel<<<1, kRadix, 0, st>>>(sc.hist, 1, nullptr);
       B200_LAUNCH_OK();
       size_t fb = (n + 255) / 256;
       if (fb > (size_t)sms * 16) fb = (size_t)sms * 16;
@@ -839,7 +869,7 @@ extern "C" int b200_sort_noalloc(const void* input, void* output, size_t n, int 
       if (blocks > (size_t)sms * 8) blocks = (size_t)sms * 8;
       sort_u8_hist_kernel<<<(unsigned)blocks, kHistThreads, 0, st>>>((const uint8_t*)input, n, sc.hist);
       B200_LAUNCH_OK();
-      sort_scan_kernel<<<1, kRadix, 0, st>>>(sc.hist, 1);
+      sort_scan_kernel<<<1, kRadix, 0, st>>>(sc.hist, 1, nullptr);
       B200_LAUNCH_OK();
       size_t fb = (n + 255) / 256;
       if (fb > (size_t)sms * 16) fb = (size_t)sms * 16;

@@ -290,6 +290,25 @@ def test_sort_runs_of_equal_digits(cuda_device):
             assert np.array_equal(d.cpu().numpy(), np.sort(k)), (run, low_bits)
 
 
+def test_sort_passes_with_one_digit_value(cuda_device):
+    """A pass whose digit is the same for every key only copies (flag from the scan kernel):
+    small-range integers, floats of one exponent, and the neighbours that must NOT take it."""
+    rng = np.random.default_rng(33)
+    for n in [5000, 1_000_003]:
+        cases = [
+            rng.integers(0, 1000, n).astype(np.int32),           # passes 2, 3 constant
+            rng.integers(-500, 500, n).astype(np.int32),         # top digits 0x00 / 0xff: two bins
+            (rng.integers(0, 256, n) << 16).astype(np.int32),    # passes 0, 1, 3 constant
+            (rng.integers(0, 2, n) << 31 | 7).astype(np.uint32).view(np.int32),  # two bins in the last pass
+            (1.0 + rng.random(n)).astype(np.float32),            # one exponent
+            np.full(n, -3, dtype=np.int32),
+        ]
+        for k in cases:
+            d = torch.from_numpy(k.copy()).to(cuda_device)
+            ops.sort_(d)
+            assert np.array_equal(d.cpu().numpy(), np.sort(k)), (n, k.dtype, k[:4])
+
+
 def test_sort_fixtures_and_host_pipeline(cuda_device, repo_root):
     for name, dt in [("int10", np.int32), ("float10", np.float32), ("uchar10", np.uint8)]:
         blob = (repo_root / "lab5/data" / name).read_bytes()
