@@ -23,6 +23,19 @@
 #include <cstdlib>
 
 #include "common.cuh"
+// ALU / FMA pipe balance (ncu: alu 52%, fma 39% of peak with every addition on the ALU pipe).
+// Same box, interleaved runs, ms at 65536^2 / 16384^2 (`tools/lab2_layout.py`):
+//   all additions on the ALU pipe                      5.94 / 0.342
+//   red "- 2^23" on the FMA pipe  (this file)          5.78 / 0.343
+//   red and blue on the FMA pipe                       5.75 / 0.348
+//   red + the final round-toward-zero addition         5.74 / 0.348  (another box: 5.74 vs 5.85 for red only)
+//   red + Gx;  Gx + rz;  rz only                       no better than red only
+//   packed fp32 (FFMA2 / FADD2 / FMUL2, B200_TMA_PACKED) 6.26 / 0.411: two pixels per instruction,
+//   27% fewer instructions, bit-identical - and slower: the packed forms cost the FMA pipe more
+//   than the two scalar instructions they replace.
+// Bands of 65536-px rows, red only vs red + rz: 2 GiB 0.661 / 0.674, 4 GiB 1.300 / 1.324, 8 GiB
+// 2.745 / 2.739, 16 GiB 5.85 / 5.74 - so the rz addition moves only for bands of kBigBandBytes up.
+#define B200_LUMA_SUB_ON_FMA_PIPE 1
 #include "roberts_math.cuh"
 
 namespace b200 {
@@ -43,6 +56,9 @@ namespace b200 {
 #endif
 #ifndef B200_TMA_OUTBUFS
 #define B200_TMA_OUTBUFS 2
+#endif
+#ifndef B200_TMA_PACKED
+#define B200_TMA_PACKED 0  // packed fp32 arithmetic (FFMA2 / FADD2 / FMUL2), two pixels per instruction: slower
 #endif
 constexpr int kTileW = 256;               // output px per tile row
 constexpr int kTileH = B200_TMA_TILE_H;   // output rows per tile
@@ -69,6 +85,9 @@ struct TmaParams {
   int l2_hints;  // evict-first for streamed rows, evict-last for the shared halo row
 };
 
+constexpr int64_t kBigBandBytes = 12ll << 30;  // input bytes from which BIG is launched (see the table above)
+
+template <bool BIG>
 __global__ void __launch_bounds__(kTmaThreads, 1)
     roberts_tma_kernel(const __grid_constant__ CUtensorMap in_map,
                        const __grid_constant__ CUtensorMap halo_map,
@@ -193,6 +212,37 @@ __global__ void __launch_bounds__(kTmaThreads, 1)
     __syncwarp();
     uint4* ob = (uint4*)(my_out + (n_stores % kOutBufs) * kOutBytes) + lane;
 
+#if B200_TMA_PACKED
+    // Two pixels per instruction: a lane's pixels 0 and 2 travel in one register pair, 1 and 3
+    // in another, and {2, 4} (4 = the right neighbour's pixel 0) in a third, so the four
+    // outputs are two calls whose operands are whole pairs.
+    f32x2 ca = luma_rgba2(px[0].x, px[0].z), cb = luma_rgba2(px[0].y, px[0].w), cc;
+    {
+      float c0, c2, c1, c3;
+      unpack2(ca, c0, c2);
+      unpack2(cb, c1, c3);
+      float c4 = __shfl_down_sync(0xffffffffu, c0, 1);
+      if (lane == 31) c4 = luma_rgba(edge[0]);
+      if (!has_right) c4 = c3;
+      cc = pack2(c2, c4);
+    }
+#pragma unroll
+    for (int r = 1; r <= kSubH; ++r) {
+      const f32x2 na = luma_rgba2(px[r].x, px[r].z), nb = luma_rgba2(px[r].y, px[r].w);
+      float n0, n2, n1, n3;
+      unpack2(na, n0, n2);
+      unpack2(nb, n1, n3);
+      float n4 = __shfl_down_sync(0xffffffffu, n0, 1);
+      if (lane == 31) n4 = luma_rgba(edge[r]);
+      if (!has_right) n4 = n3;
+      const f32x2 nc = pack2(n2, n4);
+      uint4 o;
+      roberts_pack2(ca, cb, na, nb, px[r - 1].x, px[r - 1].z, o.x, o.z);
+      roberts_pack2(cb, cc, nb, nc, px[r - 1].y, px[r - 1].w, o.y, o.w);
+      ob[(r - 1) * (kSubW / 4)] = o;
+      ca = na, cb = nb, cc = nc;
+    }
+#else
     float c0 = luma_rgba(px[0].x), c1 = luma_rgba(px[0].y), c2 = luma_rgba(px[0].z),
           c3 = luma_rgba(px[0].w);
     float c4 = __shfl_down_sync(0xffffffffu, c0, 1);
@@ -206,13 +256,14 @@ __global__ void __launch_bounds__(kTmaThreads, 1)
       if (lane == 31) n4 = luma_rgba(edge[r]);
       if (!has_right) n4 = n3;
       uint4 o;
-      o.x = roberts_pack(c0, c1, n0, n1, px[r - 1].x);
-      o.y = roberts_pack(c1, c2, n1, n2, px[r - 1].y);
-      o.z = roberts_pack(c2, c3, n2, n3, px[r - 1].z);
-      o.w = roberts_pack(c3, c4, n3, n4, px[r - 1].w);
+      o.x = roberts_pack<BIG>(c0, c1, n0, n1, px[r - 1].x);
+      o.y = roberts_pack<BIG>(c1, c2, n1, n2, px[r - 1].y);
+      o.z = roberts_pack<BIG>(c2, c3, n2, n3, px[r - 1].z);
+      o.w = roberts_pack<BIG>(c3, c4, n3, n4, px[r - 1].w);
       ob[(r - 1) * (kSubW / 4)] = o;
       c0 = n0, c1 = n1, c2 = n2, c3 = n3, c4 = n4;
     }
+#endif
     fence_proxy_async_smem();  // generic-proxy writes -> visible to the TMA engine
     __syncwarp();
     if (lane == 0) {
@@ -291,18 +342,26 @@ int roberts_tma_launch(const void* in, void* out, int w, int64_t h_local, const 
   P.l2_hints = hints;
   static PerDeviceOnce attr_once;
   if (int rc = attr_once.run("roberts_tma", [&]() -> int {
-    B200_CUDA_OK(cudaFuncSetAttribute(roberts_tma_kernel,
-                                      cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+        B200_CUDA_OK(cudaFuncSetAttribute(roberts_tma_kernel<false>,
+                                          cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+        B200_CUDA_OK(cudaFuncSetAttribute(roberts_tma_kernel<true>,
+                                          cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
         return 0;
       }))
     return rc;
   int64_t grid = device_info().sm_count;
   if (grid > P.n_tiles) grid = P.n_tiles;
-  roberts_tma_kernel<<<(int)grid, kTmaThreads, kSmemBytes, st>>>(in_map, halo_map, out_map, P);
+  if ((int64_t)w * 4 * h_local >= kBigBandBytes)
+    roberts_tma_kernel<true><<<(int)grid, kTmaThreads, kSmemBytes, st>>>(in_map, halo_map, out_map, P);
+  else
+    roberts_tma_kernel<false><<<(int)grid, kTmaThreads, kSmemBytes, st>>>(in_map, halo_map, out_map, P);
   B200_LAUNCH_OK();
   return 0;
 }
 
-int roberts_tma_preload() { return preload_kernel(roberts_tma_kernel); }
+int roberts_tma_preload() {
+  if (int rc = preload_kernel(roberts_tma_kernel<false>)) return rc;
+  return preload_kernel(roberts_tma_kernel<true>);
+}
 
 }  // namespace b200
