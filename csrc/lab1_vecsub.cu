@@ -15,8 +15,7 @@ namespace b200 {
 // hints on/off - all within 1.5% (6.14-6.27 TB/s at n = 2^25, 6.87-6.99 at 2^28); 512 x 2 with
 // hints is the best at both sizes
 constexpr int kVsThreads = 512;
-constexpr int kVsUnroll = 2;  // 2 x 32 B per array per thread in flight
-constexpr int kVsPerBlock = kVsThreads * kVsUnroll;  // 1024 vectors = 32 KB per array
+constexpr int kVsUnroll = 2;  // 2 x 32 B per array per thread in flight: 1024 vectors = 32 KB per array and CTA
 
 __device__ __forceinline__ void ld_plain_f64x4(const double* p, double (&v)[4]) {
   asm volatile("ld.global.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(v[0]), "=d"(v[1]), "=d"(v[2]), "=d"(v[3]) : "l"(p));

@@ -40,7 +40,6 @@ using namespace b200;
 namespace b200 {
 __global__ void __launch_bounds__(256) peer_copy_kernel(uint32_t* far, uint32_t* near, size_t n, int mode) {
   __shared__ __align__(128) uint32_t stage[4096];
-  __shared__ __align__(8) uint64_t bar;
   const size_t tid = blockIdx.x * (size_t)blockDim.x + threadIdx.x, nth = (size_t)gridDim.x * blockDim.x;
   if (mode == 0) {
     for (size_t i = tid; i < n; i += nth) far[i] = near[i];
@@ -51,7 +50,6 @@ __global__ void __launch_bounds__(256) peer_copy_kernel(uint32_t* far, uint32_t*
   } else if (mode == 3) {
     for (size_t i = tid; i < n / 4; i += nth) reinterpret_cast<uint4*>(near)[i] = reinterpret_cast<const uint4*>(far)[i];
   } else {
-    (void)bar;
     for (size_t c = blockIdx.x; c < n / 4096; c += gridDim.x) {
       for (int j = threadIdx.x; j < 1024; j += 256)
         reinterpret_cast<uint4*>(stage)[j] = reinterpret_cast<const uint4*>(near + c * 4096)[j];
