@@ -55,7 +55,7 @@ int main() {
         LIBOK(b200_roberts(d_in, d_out, w, h, nullptr, variant, nullptr));
     });
   };
-  float ms = 0;
+  [[maybe_unused]] float ms = 0;  // printed by the to_plot build only
   if (piped) {
     cli::PinnedRing ring;
     cli::file_to_device(in_fd, 8, d_in, bytes, ring, in_path.c_str());
@@ -79,7 +79,6 @@ int main() {
 #endif
     cli::write_image(out_path, w, h, px.data());
   }
-  (void)ms;
   cudaFree(d_in), cudaFree(d_out);
 #ifdef TO_PLOT
   printf("FINISHED!\n");

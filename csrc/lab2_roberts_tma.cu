@@ -23,19 +23,21 @@
 #include <cstdlib>
 
 #include "common.cuh"
-// ALU / FMA pipe balance (ncu: alu 52%, fma 39% of peak with every addition on the ALU pipe).
-// Same box, interleaved runs, ms at 65536^2 / 16384^2 (`tools/lab2_layout.py`):
-//   all additions on the ALU pipe                      5.94 / 0.342
-//   red "- 2^23" on the FMA pipe  (this file)          5.78 / 0.343
-//   red and blue on the FMA pipe                       5.75 / 0.348
-//   red + the final round-toward-zero addition         5.74 / 0.348  (another box: 5.74 vs 5.85 for red only)
-//   red + Gx;  Gx + rz;  rz only                       no better than red only
-//   packed fp32 (FFMA2 / FADD2 / FMUL2, B200_TMA_PACKED) 6.26 / 0.411: two pixels per instruction,
-//   27% fewer instructions, bit-identical - and slower: the packed forms cost the FMA pipe more
-//   than the two scalar instructions they replace.
-// Bands of 65536-px rows, red only vs red + rz: 2 GiB 0.661 / 0.674, 4 GiB 1.300 / 1.324, 8 GiB
-// 2.745 / 2.739, 16 GiB 5.85 / 5.74 - so the rz addition moves only for bands of kBigBandBytes up.
-#define B200_LUMA_SUB_ON_FMA_PIPE 1
+// ALU / FMA pipe balance (ncu: alu 52%, fma 39% of peak).  Additions that can be spelled
+// fma(x, 1, c) with the same single rounding can be issued to the FMA pipe instead
+// (B200_LUMA_SUB_ON_FMA_PIPE, roberts_pack<true>).  Measured two ways on 65536^2:
+//   * one launch at a time, synchronised on both sides (`tools/lab2_layout.py`, interleaved on one
+//     box): all additions on the ALU pipe 5.94 ms; red "- 2^23" on the FMA pipe 5.78; red and blue
+//     5.75; red + the final round-toward-zero addition 5.74 (but 1-2% slower on bands up to 4 GiB);
+//   * bench.py's back-to-back steps, where the 16 GiB band keeps the GPU at its power cap: 5.81-5.88
+//     for every one of these variants, in whatever order they ran (the drift of a warming GPU, 1-2%,
+//     is larger than any difference between them), and 5.94-6.00 for red + rz.
+// The sustained figure is the one that counts, so the default stays with plain additions.
+// Packed fp32 (FFMA2 / FADD2 / FMUL2, B200_TMA_PACKED: two pixels per instruction, 27% fewer
+// instructions, bit-identical) is slower in both modes: 6.26 ms / 0.411 ms at 16384^2 against 0.341.
+#ifndef B200_LUMA_SUB_ON_FMA_PIPE
+#define B200_LUMA_SUB_ON_FMA_PIPE 0
+#endif
 #include "roberts_math.cuh"
 
 namespace b200 {
@@ -85,9 +87,6 @@ struct TmaParams {
   int l2_hints;  // evict-first for streamed rows, evict-last for the shared halo row
 };
 
-constexpr int64_t kBigBandBytes = 12ll << 30;  // input bytes from which BIG is launched (see the table above)
-
-template <bool BIG>
 __global__ void __launch_bounds__(kTmaThreads, 1)
     roberts_tma_kernel(const __grid_constant__ CUtensorMap in_map,
                        const __grid_constant__ CUtensorMap halo_map,
@@ -256,10 +255,10 @@ __global__ void __launch_bounds__(kTmaThreads, 1)
       if (lane == 31) n4 = luma_rgba(edge[r]);
       if (!has_right) n4 = n3;
       uint4 o;
-      o.x = roberts_pack<BIG>(c0, c1, n0, n1, px[r - 1].x);
-      o.y = roberts_pack<BIG>(c1, c2, n1, n2, px[r - 1].y);
-      o.z = roberts_pack<BIG>(c2, c3, n2, n3, px[r - 1].z);
-      o.w = roberts_pack<BIG>(c3, c4, n3, n4, px[r - 1].w);
+      o.x = roberts_pack(c0, c1, n0, n1, px[r - 1].x);
+      o.y = roberts_pack(c1, c2, n1, n2, px[r - 1].y);
+      o.z = roberts_pack(c2, c3, n2, n3, px[r - 1].z);
+      o.w = roberts_pack(c3, c4, n3, n4, px[r - 1].w);
       ob[(r - 1) * (kSubW / 4)] = o;
       c0 = n0, c1 = n1, c2 = n2, c3 = n3, c4 = n4;
     }
@@ -342,26 +341,18 @@ int roberts_tma_launch(const void* in, void* out, int w, int64_t h_local, const 
   P.l2_hints = hints;
   static PerDeviceOnce attr_once;
   if (int rc = attr_once.run("roberts_tma", [&]() -> int {
-        B200_CUDA_OK(cudaFuncSetAttribute(roberts_tma_kernel<false>,
-                                          cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
-        B200_CUDA_OK(cudaFuncSetAttribute(roberts_tma_kernel<true>,
+        B200_CUDA_OK(cudaFuncSetAttribute(roberts_tma_kernel,
                                           cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
         return 0;
       }))
     return rc;
   int64_t grid = device_info().sm_count;
   if (grid > P.n_tiles) grid = P.n_tiles;
-  if ((int64_t)w * 4 * h_local >= kBigBandBytes)
-    roberts_tma_kernel<true><<<(int)grid, kTmaThreads, kSmemBytes, st>>>(in_map, halo_map, out_map, P);
-  else
-    roberts_tma_kernel<false><<<(int)grid, kTmaThreads, kSmemBytes, st>>>(in_map, halo_map, out_map, P);
+  roberts_tma_kernel<<<(int)grid, kTmaThreads, kSmemBytes, st>>>(in_map, halo_map, out_map, P);
   B200_LAUNCH_OK();
   return 0;
 }
 
-int roberts_tma_preload() {
-  if (int rc = preload_kernel(roberts_tma_kernel<false>)) return rc;
-  return preload_kernel(roberts_tma_kernel<true>);
-}
+int roberts_tma_preload() { return preload_kernel(roberts_tma_kernel); }
 
 }  // namespace b200
